@@ -1,0 +1,156 @@
+/*
+ * lmi_b200.h -- C ABI of the B200-native LMI query path.
+ *
+ * Drop-in boundary for the learned-navigation search behind
+ * LearnedIndex.search() of Coda-Research-Group/LearnedMetricIndex.  The reference
+ * is pure Python; the arithmetic on its hot path lives in four library calls.
+ * Each entry point below replaces one of them (file:line relative to the
+ * reference checkout):
+ *
+ *   lmi_linear / lmi_softmax_topn  <- NeuralNetwork.predict_proba
+ *                                     search/li/model.py:226-241 (Linear/ReLU
+ *                                     stack :29-79, softmax :238, topk :239) and
+ *                                     the 1-level slice bucket_order = classes[:, :B]
+ *                                     search/li/LearnedIndex.py:209-214
+ *   lmi_argmax                     <- NeuralNetwork.predict  search/li/model.py:213-224
+ *   lmi_invert                     <- filter_path_idxs       search/li/utils.py:61-65,
+ *                                     as called per bucket per round at
+ *                                     search/li/LearnedIndex.py:353
+ *   lmi_scan_topk                  <- groupby + .loc gather + faiss.knn(...,
+ *                                     METRIC_INNER_PRODUCT)
+ *                                     search/li/LearnedIndex.py:350-365
+ *   lmi_merge_topk                 <- distances = 1 - similarity, local->label id
+ *                                     mapping and the cross-round stable-argsort
+ *                                     merge  search/li/LearnedIndex.py:368-371, :125-146
+ *   lmi_scatter_rows / lmi_cast_f16<- the bucket layout the reference re-derives
+ *                                     every round from data_prediction + the
+ *                                     DataFrame index (:101-104, :350, :357),
+ *                                     materialised once as a bucket-major fp16 matrix
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no C++/torch types.
+ *   - every pointer is a DEVICE pointer owned by the caller unless the name ends
+ *     in _host; nothing is allocated or freed inside, nothing is retained.
+ *   - `stream` is a cudaStream_t passed as void*; calls only enqueue work.
+ *   - return value: 0 on success, a positive cudaError_t, or a negative LMI_E_*.
+ *     lmi_error_string() renders either.  No exceptions cross the boundary.
+ *   - thread-safety: stateless; concurrent calls on different streams are fine.
+ *   - there is no CPU fallback: every entry point launches sm_100a kernels.
+ */
+#ifndef LMI_B200_H_
+#define LMI_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LMI_B200_ABI_VERSION 1
+
+#define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
+#define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
+#define LMI_E_DRIVER (-3)      /* CUDA driver entry point (tensor map encode) unavailable */
+
+#define LMI_PER_BUCKET_K 10 /* `k` is not forwarded to _search_single_bucket (LearnedIndex.py:111-117,:334) */
+#define LMI_ITEM_WORDS 8    /* int32 words per scan work item, see lmi_invert */
+
+int lmi_version(void);
+const char *lmi_error_string(int code);
+
+/* ---- model.py ---------------------------------------------------------------- */
+
+/* y[nq,out] = act(x[nq,in] . W[out,in]^T + b), fp32 FMA.  x is fp32, or fp16 when
+ * x_is_f16 != 0 (widened exactly, as data_X_to_torch does, model.py:102-105). */
+int lmi_linear(const void *x, int x_is_f16, const float *W, const float *b, float *y,
+               int nq, int in_dim, int out_dim, int relu, void *stream);
+
+/* softmax over the C logits of each row, then the B most probable classes in
+ * descending probability (ties: lower class index first).
+ * bucket_order int32[nq,B] (== the reference's bucket_order[:, :, 0]), probs f32[nq,B]. */
+int lmi_softmax_topn(const float *logits, int nq, int C, int B,
+                     int32_t *bucket_order, float *probs, void *stream);
+
+/* argmax over the C logits of each row (first maximum), int64 out. */
+int lmi_argmax(const float *logits, int64_t n, int C, int64_t *out, void *stream);
+
+/* ---- bucket layout ------------------------------------------------------------ */
+
+/* dst[dest_row[i], :] = (fp16) src[i, :] for i < m; src is fp32 or fp16 [m,d]. */
+int lmi_scatter_rows(const void *src, int src_is_f16, const int64_t *dest_row, int64_t m, int d,
+                     void *dst_f16, void *stream);
+
+/* dst[i] = (fp16) src[i], count elements. */
+int lmi_cast_f16(const float *src, void *dst_f16, int64_t count, void *stream);
+
+/* ---- query-to-bucket inversion ------------------------------------------------ */
+
+/* Upper bound on the number of scan work items lmi_invert can emit. */
+int64_t lmi_max_items(int nq, int B, int C, int rmax);
+/* int32 words of scratch lmi_invert needs (per-chunk histograms). */
+int64_t lmi_invert_workspace_ints(int nq, int B, int C);
+
+/* Groups the nq*B (query, probe-rank) pairs by probed bucket -- ascending flat pair
+ * index p = q*B + r inside a bucket, i.e. the order filter_path_idxs yields -- and
+ * cuts the scan into work items.
+ *   bucket_order int32[nq,B]   in   (entries outside [0,C) are ignored)
+ *   bucket_off   int64[C+1]    in   row range of bucket b in the bucket-major matrix
+ *   range_len                  in   rows per work item (multiple of 64)
+ *   counts       int32[C]      out  m_b = pairs probing bucket b
+ *   offsets      int32[C+1]    out  exclusive scan of counts
+ *   pair_list    int32[nq*B]   out  flat pair index per sorted slot
+ *   slot_of_pair int32[nq*B]   out  inverse permutation (-1 for ignored pairs)
+ *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, range_idx, bucket, 0, 0}
+ *   n_items      int32[1]      out
+ *   workspace    int32[lmi_invert_workspace_ints(nq,B,C)]  scratch
+ */
+int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t *bucket_off,
+               int range_len, int32_t *counts, int32_t *offsets, int32_t *pair_list,
+               int32_t *slot_of_pair, int32_t *items, int32_t *n_items, int64_t max_items,
+               int32_t *workspace, void *stream);
+
+/* ---- candidate scan + fused per-range top-10 ---------------------------------- */
+
+/* For every work item: inner products of its <=128 queries with its rows of X
+ * (tcgen05 fp16 MMA, fp32 accumulation in TMEM, X streamed by TMA), keeping the
+ * 10 largest per query.  The full similarity matrix is never written.
+ *   X         fp16[n,d] bucket-major, 16-byte aligned, d % 64 == 0, 64 <= d <= 768
+ *   Q         fp16[nq,d]
+ *   part_sim  f32 [nq*B, rmax, 10] out  descending; -inf where fewer than 10 rows
+ *   part_row  i32 [nq*B, rmax, 10] out  row index into X; -1 where empty
+ * impl: 0 = tcgen05/TMA kernel (product path), 1 = plain CUDA-core verification
+ * kernel (tests only; any d).
+ */
+int lmi_scan_topk(const void *X, int64_t n, int d, const void *Q, int nq, int B,
+                  const int32_t *pair_list, const int32_t *items, const int32_t *n_items,
+                  int64_t max_items, int rmax, float *part_sim, int32_t *part_row,
+                  int impl, void *stream);
+
+/* ---- merge ------------------------------------------------------------------- */
+
+/* Per query: reduce each probe's per-range lists to that bucket's top-10, turn
+ * similarities into distances 1 - sim (f32), map rows to ids, pad as the reference
+ * does (undersized bucket: last id of the bucket, 1 + FLT_MAX; empty or unknown
+ * bucket: id 0, +inf), then keep the k_out smallest over all probes -- ties keep the
+ * earlier probe first (stable argsort over [previous | new], LearnedIndex.py:131-134).
+ *   ids        uint32[n]   label of each bucket-major row (the DataFrame index)
+ *   dists      f64[nq,k_out] out, nns uint32[nq,k_out] out
+ *   k_out <= 10*B.
+ */
+int lmi_merge_topk(const float *part_sim, const int32_t *part_row, const int32_t *slot_of_pair,
+                   const int32_t *bucket_order, const int64_t *bucket_off, const uint32_t *ids,
+                   int nq, int B, int C, int range_len, int rmax, int k_out,
+                   double *dists, uint32_t *nns, void *stream);
+
+/* Cross-GPU merge after the all-gather of the per-rank results: rank w's ascending
+ * lists are dists_all + w*rank_stride_d (f64[nq,k]) and nns_all + w*rank_stride_i
+ * (uint32[nq,k]) -- strides in elements, so one packed gather buffer works -- and the
+ * output is the k smallest per query (ties keep the lower rank first). world <= 32. */
+int lmi_merge_ranks(const double *dists_all, const uint32_t *nns_all, int64_t rank_stride_d,
+                    int64_t rank_stride_i, int world, int nq, int k,
+                    double *dists, uint32_t *nns, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LMI_B200_H_ */

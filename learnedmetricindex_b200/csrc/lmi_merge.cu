@@ -1,0 +1,225 @@
+// Per-query merge of the scan's partial lists (replaces distances = 1 - similarity, the
+// local-row -> DataFrame-label mapping and the cross-round stable-argsort merge,
+// search/li/LearnedIndex.py:368-371 and :125-146), plus the cross-GPU merge that follows
+// the all-gather of per-rank results.
+#include <cuda_runtime.h>
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/lmi_b200.h"
+
+namespace lmi {
+
+constexpr int MK = LMI_PER_BUCKET_K;
+
+struct Key {
+    float d;
+    int e;
+};
+__device__ __forceinline__ bool key_less(float d0, int e0, float d1, int e1) {
+    return d0 < d1 || (d0 == d1 && e0 < e1);
+}
+__device__ __forceinline__ void warp_argmin(float& d, int& e) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float od = __shfl_xor_sync(0xffffffffu, d, o);
+        const int oe = __shfl_xor_sync(0xffffffffu, e, o);
+        if (key_less(od, oe, d, e)) {
+            d = od;
+            e = oe;
+        }
+    }
+}
+
+// One warp per query.  Shared memory per warp: B*10 (dist f32, id u32) pairs.
+__global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int32_t* __restrict__ part_row,
+                                  const int32_t* __restrict__ slot_of_pair, const int32_t* __restrict__ order,
+                                  const int64_t* __restrict__ bucket_off, const uint32_t* __restrict__ ids, int nq,
+                                  int B, int C, int range_len, int rmax, int k_out, double* __restrict__ dists,
+                                  uint32_t* __restrict__ nns) {
+    extern __shared__ float sm[];
+    const int warps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * warps + warp;
+    if (q >= nq) return;
+    const int E = B * MK;
+    float* e_dist = sm + (size_t)warp * 2 * E;
+    uint32_t* e_id = reinterpret_cast<uint32_t*>(e_dist + E);
+
+    // stage 1: every probe -> that bucket's top-10 as (distance, id), padded like the reference
+    for (int r = 0; r < B; ++r) {
+        const int p = q * B + r;
+        const int b = order[p];
+        int64_t lo = 0, hi = 0;
+        if (b >= 0 && b < C) {
+            lo = bucket_off[b];
+            hi = bucket_off[b + 1];
+        }
+        if (hi <= lo) {
+            // bucket without objects: the reference's per-round buffers stay (id 0, +inf) (:340-341)
+            if (lane < MK) {
+                e_dist[r * MK + lane] = INFINITY;
+                e_id[r * MK + lane] = 0u;
+            }
+            continue;
+        }
+        const int nr = (int)((hi - lo + range_len - 1) / range_len);
+        const int slot = slot_of_pair[p];
+        // lane rr walks the (descending) list of range rr; nr <= 32 is enforced by the host
+        const size_t base = ((size_t)slot * rmax + lane) * MK;
+        int head = 0;
+        float hv = -INFINITY;
+        int hrow = -1;
+        if (lane < nr) {
+            hv = part_sim[base];
+            hrow = part_row[base];
+        }
+        const uint32_t last_id = ids[hi - 1];
+        for (int t = 0; t < MK; ++t) {
+            // arg max by (similarity desc, range asc): encode as (−sim asc, lane asc)
+            float kd = (hrow >= 0) ? -hv : INFINITY;
+            int ke = lane;
+            warp_argmin(kd, ke);
+            const bool none = !(kd < INFINITY);
+            const int win = ke;
+            const float wv = __shfl_sync(0xffffffffu, hv, win);
+            const int wrow = __shfl_sync(0xffffffffu, hrow, win);
+            if (lane == 0) {
+                if (none) {
+                    // fewer than 10 objects: faiss pads with I = -1 / D = -FLT_MAX, the reference maps
+                    // -1 to the bucket's last label and 1 - (-FLT_MAX) to FLT_MAX (:368-370)
+                    e_dist[r * MK + t] = 1.0f - (-FLT_MAX);
+                    e_id[r * MK + t] = last_id;
+                } else {
+                    e_dist[r * MK + t] = 1.0f - wv;
+                    e_id[r * MK + t] = ids[wrow];
+                }
+            }
+            if (!none && lane == win) {
+                ++head;
+                if (head < MK) {
+                    hv = part_sim[base + head];
+                    hrow = part_row[base + head];
+                } else {
+                    hrow = -1;
+                }
+            }
+        }
+    }
+    __syncwarp();
+
+    // stage 2: k_out smallest by (distance, probe rank, position) == stable argsort over the rounds
+    for (int t = 0; t < k_out; ++t) {
+        float bd = INFINITY;
+        int be = 0x7fffffff;
+        for (int e = lane; e < E; e += 32) {
+            const float dd = e_dist[e];
+            if (!(dd != dd) && key_less(dd, e, bd, be)) {  // NaN marks a taken slot
+                bd = dd;
+                be = e;
+            }
+        }
+        // +inf entries are legal candidates (empty-bucket fillers): order them by index
+        float kd = bd;
+        int ke = be;
+        warp_argmin(kd, ke);
+        if (lane == 0) {
+            if (ke == 0x7fffffff) {
+                dists[(size_t)q * k_out + t] = INFINITY;
+                nns[(size_t)q * k_out + t] = 0u;
+            } else {
+                dists[(size_t)q * k_out + t] = (double)e_dist[ke];
+                nns[(size_t)q * k_out + t] = e_id[ke];
+                e_dist[ke] = __int_as_float(0x7fc00000);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// rank w's ascending lists live at d_all + w*stride_d / i_all + w*stride_i, each [nq, k];
+// output [nq, k]; ties keep the lower rank, then the lower position
+__global__ void merge_ranks_kernel(const double* __restrict__ d_all, const uint32_t* __restrict__ i_all,
+                                   int64_t stride_d, int64_t stride_i, int world, int nq, int k,
+                                   double* __restrict__ dists, uint32_t* __restrict__ nns) {
+    const int warps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * warps + warp;
+    if (q >= nq) return;
+    // lane w (< world) walks rank w's ascending list; world <= 32
+    int head = 0;
+    const size_t base_d = (size_t)lane * stride_d + (size_t)q * k;
+    const size_t base_i = (size_t)lane * stride_i + (size_t)q * k;
+    double hv = (lane < world) ? d_all[base_d] : INFINITY;
+    bool live = lane < world;
+    for (int t = 0; t < k; ++t) {
+        double kd = hv;
+        int ke = live ? lane : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double od = __shfl_xor_sync(0xffffffffu, kd, o);
+            const int oe = __shfl_xor_sync(0xffffffffu, ke, o);
+            if (oe != 0x7fffffff && (ke == 0x7fffffff || od < kd || (od == kd && oe < ke))) {
+                kd = od;
+                ke = oe;
+            }
+        }
+        if (ke == 0x7fffffff) {
+            if (lane == 0) {
+                dists[(size_t)q * k + t] = INFINITY;
+                nns[(size_t)q * k + t] = 0u;
+            }
+            continue;
+        }
+        if (lane == ke) {
+            dists[(size_t)q * k + t] = hv;
+            nns[(size_t)q * k + t] = i_all[base_i + head];
+            ++head;
+            if (head < k) hv = d_all[base_d + head];
+            else live = false;
+        }
+    }
+}
+
+}  // namespace lmi
+
+extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, const int32_t* slot_of_pair,
+                              const int32_t* bucket_order, const int64_t* bucket_off, const uint32_t* ids, int nq,
+                              int B, int C, int range_len, int rmax, int k_out, double* dists, uint32_t* nns,
+                              void* stream) {
+    if (!part_sim || !part_row || !slot_of_pair || !bucket_order || !bucket_off || !ids || !dists || !nns)
+        return LMI_E_BADARG;
+    if (nq < 0 || B <= 0 || C <= 0 || range_len <= 0 || rmax <= 0 || k_out <= 0) return LMI_E_BADARG;
+    if (k_out > B * lmi::MK) return LMI_E_BADARG;
+    if (rmax > 32) return LMI_E_UNSUPPORTED;
+    if (nq == 0) return 0;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t per_warp = (size_t)2 * B * lmi::MK * sizeof(float);
+    int warps = 4;
+    while (warps > 1 && per_warp * warps > 160 * 1024) warps >>= 1;
+    const size_t smem = per_warp * warps;
+    if (smem > 200 * 1024) return LMI_E_UNSUPPORTED;
+    if (smem > 48 * 1024) {
+        cudaError_t e =
+            cudaFuncSetAttribute(lmi::merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+    }
+    const int grid = (nq + warps - 1) / warps;
+    lmi::merge_topk_kernel<<<grid, warps * 32, smem, st>>>(part_sim, part_row, slot_of_pair, bucket_order, bucket_off,
+                                                           ids, nq, B, C, range_len, rmax, k_out, dists, nns);
+    return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lmi_merge_ranks(const double* dists_all, const uint32_t* nns_all, int64_t rank_stride_d,
+                               int64_t rank_stride_i, int world, int nq, int k, double* dists, uint32_t* nns,
+                               void* stream) {
+    if (!dists_all || !nns_all || !dists || !nns || world <= 0 || nq < 0 || k <= 0) return LMI_E_BADARG;
+    if (world > 32) return LMI_E_UNSUPPORTED;
+    if (nq == 0) return 0;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int warps = 4;
+    lmi::merge_ranks_kernel<<<(nq + warps - 1) / warps, warps * 32, 0, st>>>(dists_all, nns_all, rank_stride_d,
+                                                                           rank_stride_i, world, nq, k, dists, nns);
+    return static_cast<int>(cudaGetLastError());
+}

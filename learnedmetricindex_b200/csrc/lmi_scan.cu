@@ -1,0 +1,368 @@
+// Candidate distance scan with a fused per-query top-10 (replaces groupby + .loc gather +
+// faiss.knn(..., METRIC_INNER_PRODUCT), search/li/LearnedIndex.py:350-365).
+//
+// Work item = (bucket, row range of <= range_len rows, tile of <= 128 probing queries).
+// Persistent CTAs (one per SM) walk the item list round-robin.  Per item:
+//   * the 128 query rows are gathered straight from the fp16 query matrix into TENSOR
+//     MEMORY (tcgen05.st), where they stay as the A operand for the whole range
+//     (K = d <= 768 fp16 -> <= 384 TMEM columns); the queries are never re-streamed;
+//   * the bucket's rows stream HBM -> shared memory by TMA (64 rows x 128 B boxes,
+//     SWIZZLE_128B, ring of SCAN_STAGES x 8 KB) and are the B operand;
+//   * tcgen05.mma kind::f16 (fp16 x fp16 -> fp32) M=128, N=64, K=16 accumulates a
+//     128 x 64 score tile in TMEM, double buffered (2 x 64 columns);
+//   * four epilogue warps read the tile (tcgen05.ld, thread == query row) and keep a
+//     threshold-gated sorted top-10 in registers; the score matrix never leaves the SM.
+// Roles: warps 0-3 epilogue (+ query gather), warp 4 TMA producer, warp 5 MMA issuer.
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/lmi_b200.h"
+#include "lmi_ptx.cuh"
+
+namespace lmi {
+
+constexpr int SCAN_M = 128;        // queries per item (TMEM lanes)
+constexpr int SCAN_N = 64;         // bucket rows per MMA tile
+constexpr int SCAN_KBLK = 64;      // fp16 per 128-byte shared-memory row
+constexpr int SCAN_STAGE_BYTES = SCAN_N * 128;
+constexpr int SCAN_STAGES = 24;
+constexpr int SCAN_THREADS = 192;
+constexpr int SCAN_MAX_D = 768;
+constexpr uint32_t TMEM_COLS = 512;
+constexpr uint32_t TMEM_ACC_COL = SCAN_MAX_D / 2;  // A: columns [0,384); accumulators: [384,448), [448,512)
+constexpr int TOPK = LMI_PER_BUCKET_K;
+constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
+
+struct ScanBarriers {
+    uint64_t full[SCAN_STAGES];
+    uint64_t empty[SCAN_STAGES];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint64_t q_ready;
+    uint32_t tmem_base;
+};
+static_assert(sizeof(ScanBarriers) <= 512, "barrier block too large");
+
+// sorted (descending) top-10 kept in registers; strict '>' keeps the earlier row on ties
+struct TopK {
+    float s[TOPK];
+    int32_t i[TOPK];
+    __device__ __forceinline__ void reset() {
+#pragma unroll
+        for (int t = 0; t < TOPK; ++t) {
+            s[t] = -INFINITY;
+            i[t] = -1;
+        }
+    }
+    __device__ __forceinline__ void insert(float v, int32_t idx) {
+        s[TOPK - 1] = v;
+        i[TOPK - 1] = idx;
+#pragma unroll
+        for (int t = TOPK - 1; t > 0; --t) {
+            const bool sw = s[t] > s[t - 1];
+            const float fs = sw ? s[t - 1] : s[t];
+            const float bs = sw ? s[t] : s[t - 1];
+            const int32_t fi = sw ? i[t - 1] : i[t];
+            const int32_t bi = sw ? i[t] : i[t - 1];
+            s[t] = fs;
+            s[t - 1] = bs;
+            i[t] = fi;
+            i[t - 1] = bi;
+        }
+    }
+    __device__ __forceinline__ void offer(float v, int32_t idx) {
+        if (v > s[TOPK - 1]) insert(v, idx);
+    }
+};
+
+__device__ __forceinline__ void store_topk(const TopK& tk, float* __restrict__ part_sim,
+                                           int32_t* __restrict__ part_row, size_t out) {
+#pragma unroll
+    for (int t = 0; t < TOPK; t += 2) {
+        *reinterpret_cast<float2*>(part_sim + out + t) = make_float2(tk.s[t], tk.s[t + 1]);
+        *reinterpret_cast<int2*>(part_row + out + t) = make_int2(tk.i[t], tk.i[t + 1]);
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS, 1)
+scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __restrict__ Q,
+                    const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
+                    const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int rmax,
+                    float* __restrict__ part_sim, int32_t* __restrict__ part_row) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    ScanBarriers* bars = reinterpret_cast<ScanBarriers*>(stages + (size_t)SCAN_STAGES * SCAN_STAGE_BYTES);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int KB = d / SCAN_KBLK;
+    int n_items = *n_items_ptr;
+    if ((int64_t)n_items > max_items) n_items = (int)max_items;
+
+    if (warp == 4 && lane == 0) {
+        ptx::tma_prefetch_desc(&tmap);
+        for (int s = 0; s < SCAN_STAGES; ++s) {
+            ptx::mbar_init(&bars->full[s], 1);
+            ptx::mbar_init(&bars->empty[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            ptx::mbar_init(&bars->acc_full[b], 1);
+            ptx::mbar_init(&bars->acc_empty[b], SCAN_M);
+        }
+        ptx::mbar_init(&bars->q_ready, SCAN_M);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 5) {
+        ptx::tmem_alloc(&bars->tmem_base, TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = bars->tmem_base;
+
+    if (warp == 4) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            const uint64_t policy = ptx::policy_evict_normal();
+            uint32_t stage = 0, phase = 0;
+            for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+                const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+                const int row0 = w0.x, nrows = w0.y;
+                const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+                for (int t = 0; t < ntiles; ++t) {
+                    for (int kb = 0; kb < KB; ++kb) {
+                        ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
+                        ptx::mbar_arrive_expect_tx(&bars->full[stage], SCAN_STAGE_BYTES);
+                        ptx::tma_load_2d(stages + (size_t)stage * SCAN_STAGE_BYTES, &tmap, kb * SCAN_KBLK,
+                                         row0 + t * SCAN_N, &bars->full[stage], policy);
+                        if (++stage == SCAN_STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 5) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
+            uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0;
+            for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+                const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+                const int nrows = w0.y;
+                const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+                ptx::mbar_wait(&bars->q_ready, item_parity);
+                item_parity ^= 1;
+                ptx::tc_fence_after();
+                for (int t = 0; t < ntiles; ++t, ++tcount) {
+                    const uint32_t buf = tcount & 1;
+                    ptx::mbar_wait(&bars->acc_empty[buf], ((tcount >> 1) & 1) ^ 1);
+                    ptx::tc_fence_after();
+                    const uint32_t d_tmem = tmem + TMEM_ACC_COL + buf * SCAN_N;
+                    for (int kb = 0; kb < KB; ++kb) {
+                        ptx::mbar_wait(&bars->full[stage], phase);
+                        ptx::tc_fence_after();
+                        const uint32_t b_base = ptx::smem_u32(stages + (size_t)stage * SCAN_STAGE_BYTES);
+#pragma unroll
+                        for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                            const uint64_t b_desc = ptx::umma_desc_sw128_kmajor(b_base + k * 32);
+                            const uint32_t a_tmem = tmem + kb * (SCAN_KBLK / 2) + k * 8;
+                            ptx::mma_f16_ts(d_tmem, a_tmem, b_desc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        ptx::mma_commit(&bars->empty[stage]);
+                        if (++stage == SCAN_STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+                    ptx::mma_commit(&bars->acc_full[buf]);
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== epilogue warps (thread == query row) =====================
+        const int row = warp * 32 + lane;
+        const uint32_t lane_field = static_cast<uint32_t>(warp * 32) << 16;
+        uint32_t tcount = 0;
+        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+            const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+            const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
+            const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, range_idx = w1.x;
+            const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+            const bool valid = row < mvalid;
+
+            // gather this item's query rows into TMEM (all MMAs of the previous item have
+            // completed: this warp consumed its last accumulator tile)
+            const int q = valid ? (pair_list[slot0 + row] / B) : 0;
+            const uint4* qsrc = reinterpret_cast<const uint4*>(Q + (size_t)q * d);
+            for (int c = 0; c < KB; ++c) {
+                uint32_t r[32];
+                if (valid) {
+#pragma unroll
+                    for (int v = 0; v < 8; ++v) {
+                        const uint4 u = __ldg(qsrc + c * 8 + v);
+                        r[4 * v + 0] = u.x;
+                        r[4 * v + 1] = u.y;
+                        r[4 * v + 2] = u.z;
+                        r[4 * v + 3] = u.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int v = 0; v < 32; ++v) r[v] = 0u;
+                }
+                ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), r);
+            }
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(&bars->q_ready);
+
+            TopK tk;
+            tk.reset();
+            for (int t = 0; t < ntiles; ++t, ++tcount) {
+                const uint32_t buf = tcount & 1;
+                ptx::mbar_wait(&bars->acc_full[buf], (tcount >> 1) & 1);
+                ptx::tc_fence_after();
+                uint32_t v0[32], v1[32];
+                const uint32_t taddr = tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N;
+                ptx::tmem_ld32(taddr, v0);
+                ptx::tmem_ld32(taddr + 32, v1);
+                ptx::tmem_ld_wait();
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(&bars->acc_empty[buf]);
+
+                const int base_row = row0 + t * SCAN_N;
+                const int live = nrows - t * SCAN_N;  // rows of this tile that belong to the range
+                if (live >= SCAN_N) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) tk.offer(__uint_as_float(v0[j]), base_row + j);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) tk.offer(__uint_as_float(v1[j]), base_row + 32 + j);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < live) tk.offer(__uint_as_float(v0[j]), base_row + j);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (32 + j < live) tk.offer(__uint_as_float(v1[j]), base_row + 32 + j);
+                }
+            }
+            if (valid) store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * rmax + range_idx) * TOPK);
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem, TMEM_COLS);
+    }
+}
+
+// Verification kernel (tests only): same item list, same top-k bookkeeping, plain fp32
+// FMA dot products on CUDA cores.  One block per item, thread == query row.
+__global__ void __launch_bounds__(SCAN_M)
+scan_topk_simt_kernel(const __half* __restrict__ X, const __half* __restrict__ Q,
+                      const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
+                      const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int rmax,
+                      float* __restrict__ part_sim, int32_t* __restrict__ part_row) {
+    extern __shared__ __half xs[];  // one row of X
+    int n_items = *n_items_ptr;
+    if ((int64_t)n_items > max_items) n_items = (int)max_items;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+        const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
+        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, range_idx = w1.x;
+        const int row = threadIdx.x;
+        const bool valid = row < mvalid;
+        const int q = valid ? (pair_list[slot0 + row] / B) : 0;
+        const __half* qrow = Q + (size_t)q * d;
+        TopK tk;
+        tk.reset();
+        for (int r = 0; r < nrows; ++r) {
+            __syncthreads();
+            const __half* xrow = X + (size_t)(row0 + r) * d;
+            for (int c = threadIdx.x; c < d; c += blockDim.x) xs[c] = xrow[c];
+            __syncthreads();
+            if (valid) {
+                float acc = 0.f;
+                for (int c = 0; c < d; ++c) acc = fmaf(__half2float(qrow[c]), __half2float(xs[c]), acc);
+                tk.offer(acc, row0 + r);
+            }
+        }
+        if (valid) store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * rmax + range_idx) * TOPK);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+    return fn;
+}
+
+}  // namespace lmi
+
+extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int nq, int B,
+                             const int32_t* pair_list, const int32_t* items, const int32_t* n_items,
+                             int64_t max_items, int rmax, float* part_sim, int32_t* part_row, int impl,
+                             void* stream) {
+    if (!X || !Q || !pair_list || !items || !n_items || !part_sim || !part_row) return LMI_E_BADARG;
+    if (n <= 0 || d <= 0 || nq <= 0 || B <= 0 || rmax <= 0 || max_items <= 0) return LMI_E_BADARG;
+    if (n > 0x7fffffffLL) return LMI_E_UNSUPPORTED;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+
+    if (impl == 1) {
+        const int grid = (int)(max_items < (int64_t)sms * 8 ? max_items : (int64_t)sms * 8);
+        lmi::scan_topk_simt_kernel<<<grid, lmi::SCAN_M, (size_t)d * sizeof(__half), st>>>(
+            static_cast<const __half*>(X), static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d,
+            rmax, part_sim, part_row);
+        return static_cast<int>(cudaGetLastError());
+    }
+    if (impl != 0) return LMI_E_BADARG;
+    if (d % lmi::SCAN_KBLK != 0 || d > lmi::SCAN_MAX_D) return LMI_E_UNSUPPORTED;
+    if ((reinterpret_cast<uintptr_t>(X) & 15) != 0 || (reinterpret_cast<uintptr_t>(Q) & 15) != 0) return LMI_E_BADARG;
+
+    lmi::EncodeTiledFn encode = lmi::get_encode_fn();
+    if (!encode) return LMI_E_DRIVER;
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)n};
+    const cuuint64_t gstride[1] = {(cuuint64_t)d * sizeof(__half)};
+    const cuuint32_t box[2] = {(cuuint32_t)lmi::SCAN_KBLK, (cuuint32_t)lmi::SCAN_N};
+    const cuuint32_t estride[2] = {1, 1};
+    CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(X), gdim, gstride, box, estride,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) return LMI_E_DRIVER;
+
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(lmi::scan_topk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)lmi::SCAN_SMEM_BYTES);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int grid = (int)(max_items < (int64_t)sms ? max_items : (int64_t)sms);
+    lmi::scan_topk_tc_kernel<<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
+        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, rmax, part_sim, part_row);
+    return static_cast<int>(cudaGetLastError());
+}

@@ -1,0 +1,133 @@
+"""Host-side mirror of the reference's ``li.model`` for INFERENCE (search/li/model.py).
+
+``NeuralNetwork`` keeps the reference's public surface on the query path --
+``predict_proba(X) -> (probs f32[nq,C] descending, classes i64[nq,C])`` (:226-241) and
+``predict(X) -> argmax`` (:213-224) -- but the arithmetic runs in the sm_100a kernels
+behind ``lmi_linear`` / ``lmi_softmax_topn`` / ``lmi_argmax``.  Training
+(``train`` / ``train_batch``, :166-211) is the offline build and out of scope.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _native
+
+# hidden widths of ``supported_models`` -- search/li/model.py:29-79
+HIDDEN_LAYERS = {
+    "MLP": [128], "MLP-2": [64], "MLP-3": [256], "MLP-4": [512], "MLP-5": [256, 128],
+    "MLP-6": [32], "MLP-7": [16], "MLP-8": [8], "MLP-9": [8, 16],
+}
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def data_X_to_torch(data) -> torch.Tensor:
+    """search/li/model.py:102-105."""
+    return torch.from_numpy(np.array(data).astype(np.float32))
+
+
+def get_device() -> torch.device:
+    """search/li/model.py:115-127 -- but there is no CPU path here: CUDA is required."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("learnedmetricindex_b200 needs a CUDA device (no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def to_device_matrix(x, device: torch.device) -> torch.Tensor:
+    """Host ndarray / torch tensor -> contiguous device matrix, fp16 kept as fp16 (widening
+    to f32 happens exactly inside the kernels), everything else as f32 (model.py:104)."""
+    if isinstance(x, torch.Tensor):
+        t = x
+    else:
+        a = np.asarray(x)
+        if a.dtype not in (np.float16, np.float32):
+            a = a.astype(np.float32)
+        t = torch.from_numpy(np.ascontiguousarray(a))
+    if t.dtype not in (torch.float16, torch.float32):
+        t = t.float()
+    return t.to(device, non_blocking=True).contiguous()
+
+
+class NeuralNetwork:
+    """Inference-only mirror of ``li.model.NeuralNetwork`` holding the weights on the GPU."""
+
+    def __init__(self, layers: Sequence[Tuple[object, object]], model_type: Optional[str] = None,
+                 device: Optional[torch.device] = None):
+        self.device = device or get_device()
+        self.model_type = model_type
+        self.layers: List[Tuple[torch.Tensor, torch.Tensor]] = []
+        for W, b in layers:
+            Wt = torch.as_tensor(np.asarray(W) if not isinstance(W, torch.Tensor) else W)
+            bt = torch.as_tensor(np.asarray(b) if not isinstance(b, torch.Tensor) else b)
+            self.layers.append((Wt.detach().to(self.device, torch.float32).contiguous(),
+                                bt.detach().to(self.device, torch.float32).contiguous()))
+        for (W0, _), (W1, _) in zip(self.layers[:-1], self.layers[1:]):
+            assert W1.shape[1] == W0.shape[0], "layer shapes do not chain"
+        self.input_dim = self.layers[0][0].shape[1]
+        self.n_output_neurons = self.layers[-1][0].shape[0]
+
+    # -- construction from the reference's objects ------------------------------------
+    @classmethod
+    def from_reference(cls, nn, device=None) -> "NeuralNetwork":
+        """From a reference ``NeuralNetwork`` (``nn.model.layers`` is the ``Sequential`` of
+        ``Linear``/``ReLU``, model.py:94) or from anything exposing ``state_dict()``."""
+        if isinstance(nn, cls):
+            return nn
+        module = getattr(nn, "model", nn)
+        sd = module.state_dict()
+        idx = sorted({int(k.split(".")[-2]) for k in sd if k.endswith(".weight")})
+        prefix = "layers." if any(k.startswith("layers.") for k in sd) else ""
+        layers = [(sd[f"{prefix}{i}.weight"], sd[f"{prefix}{i}.bias"]) for i in idx]
+        return cls(layers, device=device)
+
+    # -- kernels ----------------------------------------------------------------------
+    def logits(self, x: torch.Tensor) -> torch.Tensor:
+        """``Model.forward`` (model.py:97-99) on a device matrix (fp16 or f32)."""
+        L = _native.lib()
+        assert x.is_cuda and x.dim() == 2 and x.is_contiguous()
+        assert x.shape[1] == self.input_dim, (x.shape, self.input_dim)
+        nq = x.shape[0]
+        h = x
+        for li, (W, b) in enumerate(self.layers):
+            out = torch.empty((nq, W.shape[0]), dtype=torch.float32, device=self.device)
+            _native.check(L.lmi_linear(h.data_ptr(), int(h.dtype == torch.float16), W.data_ptr(), b.data_ptr(),
+                                       out.data_ptr(), nq, W.shape[1], W.shape[0],
+                                       int(li + 1 < len(self.layers)), _stream_ptr()), "lmi_linear")
+            h = out
+        return h
+
+    def topn_device(self, x: torch.Tensor, n_top: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        """(bucket ids int32[nq,n_top], probabilities f32[nq,n_top]) on the device."""
+        L = _native.lib()
+        logits = self.logits(x)
+        nq, C = logits.shape
+        order = torch.empty((nq, n_top), dtype=torch.int32, device=self.device)
+        probs = torch.empty((nq, n_top), dtype=torch.float32, device=self.device)
+        _native.check(L.lmi_softmax_topn(logits.data_ptr(), nq, C, n_top, order.data_ptr(), probs.data_ptr(),
+                                         _stream_ptr()), "lmi_softmax_topn")
+        return order, probs
+
+    def predict_proba(self, data_X) -> Tuple[np.ndarray, np.ndarray]:
+        """search/li/model.py:226-241: all classes, most probable first."""
+        x = to_device_matrix(data_X, self.device)
+        order, probs = self.topn_device(x, self.n_output_neurons)
+        return probs.cpu().numpy(), order.cpu().numpy().astype(np.int64)
+
+    def predict_device(self, x: torch.Tensor, chunk: int = 1 << 20) -> torch.Tensor:
+        L = _native.lib()
+        out = torch.empty(x.shape[0], dtype=torch.int64, device=self.device)
+        for s in range(0, x.shape[0], chunk):
+            xs = x[s : s + chunk]
+            logits = self.logits(xs)
+            _native.check(L.lmi_argmax(logits.data_ptr(), logits.shape[0], logits.shape[1],
+                                       out[s : s + chunk].data_ptr(), _stream_ptr()), "lmi_argmax")
+        return out
+
+    def predict(self, data_X) -> np.ndarray:
+        """search/li/model.py:213-224: argmax class per row."""
+        return self.predict_device(to_device_matrix(data_X, self.device)).cpu().numpy()

@@ -1,0 +1,95 @@
+"""CPU-side checks: the C-ABI library builds, loads and exports every symbol the header
+declares; host-side planning logic."""
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "lmi_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(lmi_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_builds_loads_and_exports_header_symbols():
+    from learnedmetricindex_b200 import _native
+
+    _native.build_library()
+    lib = _native.lib()
+    declared = _declared_symbols()
+    assert len(declared) >= 12
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/lmi_b200.h but not exported"
+    assert set(declared) == set(_native.EXPORTED_SYMBOLS), "ctypes signatures out of sync with the header"
+    assert lib.lmi_version() == 1
+    assert lib.lmi_error_string(0) == b"success"
+    assert b"bad argument" in lib.lmi_error_string(-1)
+    # size helpers are pure host functions
+    assert lib.lmi_max_items(10000, 4, 120, 5) >= 5 * (40000 // 128 + 120)
+    assert lib.lmi_invert_workspace_ints(10000, 4, 120) % 120 == 0
+
+
+def test_sass_is_blackwell_native():
+    """tcgen05 / TMA must be what the scan kernel compiles to (no legacy HMMA path)."""
+    import shutil
+    import subprocess
+
+    from learnedmetricindex_b200 import _native
+
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.isfile(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    _native.build_library()
+    sass = subprocess.run([cuobjdump, "-sass", _native.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in sass
+    for needle in ("UTCHMMA", "UTMALDG", "LDTM", "STTM"):
+        assert needle in sass, needle
+    assert "HMMA." not in sass.replace("UTCHMMA", "")
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from learnedmetricindex_b200 import _native
+
+    monkeypatch.setattr(_native, "_lib", None)
+    monkeypatch.setattr(_native, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        _native.lib()
+
+
+def test_no_cuda_fails_loudly():
+    import torch
+
+    from learnedmetricindex_b200 import model
+
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        model.get_device()
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "learnedmetricindex_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.replace("oracle/", "").lower() or f == "synthetic.py" and False, \
+                    f"{f} mentions the oracle"
+
+
+@pytest.mark.parametrize("nq,B,C,n,maxb", [
+    (10000, 4, 120, 10_000_000, 120_000), (1, 1, 120, 10_000_000, 120_000), (1, 4, 120, 10_000_000, 90_000),
+    (100_000, 120, 120, 10_000_000, 120_000), (10000, 4, 120, 100_000, 1100), (7, 3, 5, 40, 17),
+])
+def test_plan_scan(nq, B, C, n, maxb):
+    from learnedmetricindex_b200 import plan_scan
+    from learnedmetricindex_b200.LearnedIndex import MAX_RANGES
+
+    length, rmax = plan_scan(nq, B, C, n, maxb)
+    assert length % 64 == 0 and length >= 64
+    assert 1 <= rmax <= MAX_RANGES
+    assert rmax * length >= maxb  # every bucket is covered
+    assert (rmax - 1) * length < maxb or rmax == 1

@@ -1,0 +1,216 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the golden
+fixtures written from the reference.  Needs a B200: run with ``-m gpu``.
+
+Tolerances (BASELINE.json north_star): probed-bucket lists bit-exact except where bucket
+probabilities tie within 1e-6; distances within 1e-3 relative; ids identical except at
+distance ties.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import lmi_oracle as orc
+from tests.golden_util import GoldenCase, assert_search_parity, case_names
+
+pytestmark = pytest.mark.gpu
+
+
+def _index(layers, C, scan_impl=0):
+    from learnedmetricindex_b200 import LearnedIndex
+
+    return LearnedIndex(layers, {}, [(i,) for i in range(C)], scan_impl=scan_impl)
+
+
+def _order_rows_equal(got, exp, probs, tol=1e-6):
+    """Rows whose probed-bucket list equals the oracle's; a differing row must be explained
+    by a probability tie (adjacent oracle probabilities within ``tol``)."""
+    same = (got == exp).all(axis=1)
+    for r in np.flatnonzero(~same):
+        B = got.shape[1]
+        p = probs[r]
+        cols = np.flatnonzero(got[r] != exp[r])
+        lo, hi = cols.min(), min(cols.max() + 1, len(p) - 1)
+        assert np.abs(np.diff(p[lo : hi + 1])).min() <= tol or (B < len(p) and abs(p[B - 1] - p[B]) <= tol), (
+            f"row {r}: bucket order differs without a probability tie: {got[r]} vs {exp[r]}")
+    return same
+
+
+@pytest.mark.parametrize("name", case_names())
+def test_mlp_matches_reference_golden(name):
+    c = GoldenCase(name)
+    C = c.n_categories[0]
+    li = _index(c.layers, C)
+    probs, classes = li.root_model.predict_proba(c.Q)
+    assert probs.dtype == np.float32 and classes.dtype == np.int64 and classes.shape == c.classes.shape
+    np.testing.assert_allclose(probs, c.probs, rtol=2e-5, atol=1e-7)
+    _order_rows_equal(classes, c.classes, c.probs)
+    # predict == argmax
+    pred = li.root_model.predict(c.X)
+    exp = orc.predict(c.layers, orc.to_f32_tensor(c.X))
+    assert (pred == exp).mean() > 0.999
+
+
+def test_invert_matches_numpy():
+    from learnedmetricindex_b200 import _native
+
+    L = _native.lib()
+    rs = np.random.RandomState(5)
+    for nq, B, C, rng_len in [(1, 1, 7, 64), (37, 3, 11, 128), (5000, 4, 120, 1024), (20000, 16, 50, 4096)]:
+        order = np.stack([rs.permutation(C)[:B] for _ in range(nq)]).astype(np.int32)
+        order[rs.rand(nq, B) < 0.02] = -1  # ignored entries
+        sizes = rs.randint(0, 3000, C)
+        sizes[rs.rand(C) < 0.1] = 0
+        off = np.zeros(C + 1, dtype=np.int64)
+        off[1:] = np.cumsum(sizes)
+        rmax = max(1, int(-(-sizes.max() // rng_len)))
+        dev = torch.device("cuda")
+        t = lambda a: torch.from_numpy(a).to(dev)
+        P = nq * B
+        max_items = int(L.lmi_max_items(nq, B, C, rmax))
+        d_counts = torch.empty(C, dtype=torch.int32, device=dev)
+        d_off = torch.empty(C + 1, dtype=torch.int32, device=dev)
+        d_pl = torch.full((P,), -7, dtype=torch.int32, device=dev)
+        d_sop = torch.full((P,), -7, dtype=torch.int32, device=dev)
+        d_items = torch.zeros(max_items * 8, dtype=torch.int32, device=dev)
+        d_n = torch.zeros(1, dtype=torch.int32, device=dev)
+        work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
+        d_order, d_boff = t(order), t(off)
+        _native.check(L.lmi_invert(d_order.data_ptr(), nq, B, C, d_boff.data_ptr(), rng_len, d_counts.data_ptr(),
+                                   d_off.data_ptr(), d_pl.data_ptr(), d_sop.data_ptr(), d_items.data_ptr(),
+                                   d_n.data_ptr(), max_items, work.data_ptr(), 0))
+        torch.cuda.synchronize()
+        flat = order.reshape(-1)
+        valid = flat >= 0
+        exp_counts = np.bincount(flat[valid], minlength=C)
+        assert np.array_equal(d_counts.cpu().numpy(), exp_counts)
+        exp_off = np.concatenate(([0], np.cumsum(exp_counts)))
+        assert np.array_equal(d_off.cpu().numpy(), exp_off)
+        # stable: ascending flat pair index inside a bucket == np.where order of filter_path_idxs
+        exp_pl = np.argsort(np.where(valid, flat, C), kind="stable")[: valid.sum()]
+        assert np.array_equal(d_pl.cpu().numpy()[: valid.sum()], exp_pl)
+        sop = d_sop.cpu().numpy()
+        assert np.array_equal(sop[exp_pl], np.arange(valid.sum()))
+        assert (sop[~valid] == -1).all()
+        # work items: every (bucket with m>0 and rows>0) x range x query tile exactly once
+        n_items = int(d_n.item())
+        items = d_items.cpu().numpy().reshape(-1, 8)[:n_items]
+        exp_items = []
+        for b in range(C):
+            m, s = exp_counts[b], sizes[b]
+            if m == 0 or s == 0:
+                continue
+            for r in range(-(-s // rng_len)):
+                for tq in range(-(-m // 128)):
+                    exp_items.append((off[b] + r * rng_len, min(rng_len, s - r * rng_len), exp_off[b] + tq * 128,
+                                      min(128, m - tq * 128), r, b, 0, 0))
+        assert n_items == len(exp_items) <= max_items
+        assert np.array_equal(items, np.array(exp_items, dtype=np.int32).reshape(-1, 8))
+
+
+@pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("name", case_names())
+def test_search_matches_reference_golden(name, impl):
+    c = GoldenCase(name)
+    C = c.n_categories[0]
+    import pandas as pd
+
+    li = _index(c.layers, C, scan_impl=impl)
+    df_nav = pd.DataFrame(c.X, index=pd.Index(c.ids))
+    df_search = pd.DataFrame(c.X, index=pd.Index(c.ids))
+    for B, k in c.runs:
+        exp_order, exp_d, exp_i = c.expected(B, k)
+        d, i, times = li.search(df_nav, c.Q, df_search, c.Q, c.data_prediction, c.n_categories, n_buckets=B, k=k)
+        assert d.dtype == np.float64 and i.dtype == np.uint32
+        got_order = li.last_bucket_order.cpu().numpy()
+        same = _order_rows_equal(got_order, exp_order[:, :, 0], c.probs)
+        assert_search_parity(d[same], i[same], exp_d[same], exp_i[same],
+                             what=f"{name} B={B} k={k} impl={impl}")
+        assert set(times) >= {"inference", "search_within_buckets", "seq_search", "sort", "search"}
+
+
+def _synthetic(n, nq, C, seed_centres=300, steps=80):
+    from learnedmetricindex_b200 import synthetic as syn
+
+    spec = syn.MixtureSpec(n_centres=seed_centres)
+    X = syn.make_vectors(n, spec)
+    Q = syn.make_vectors(nq, spec, stream=1)
+    layers, pred = syn.build_standin_index(X, C, steps=steps)
+    return X.numpy(), Q.numpy(), syn.layers_to_numpy(layers), pred.numpy()
+
+
+@pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
+def test_search_matches_oracle_medium(impl):
+    """Ragged real-sized buckets, several ranges per bucket, partial query tiles."""
+    n, nq, C, B = 60_000, 1500, 24, 4
+    X, Q, layers, pred = _synthetic(n, nq, C)
+    li = _index(layers, C, scan_impl=impl)
+    d, i, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=B, k=10)
+    exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=10)
+    probs, _ = orc.predict_proba(layers, orc.to_f32_tensor(Q))
+    same = _order_rows_equal(li.last_bucket_order.cpu().numpy(), exp_order[:, :, 0], probs)
+    assert same.mean() > 0.995
+    assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what=f"medium impl={impl}")
+    gt_d, gt_i = orc.brute_force(Q, X)
+    r_gpu = orc.get_recall(i.astype(np.int64), gt_i, 10)
+    r_cpu = orc.get_recall(exp_i.astype(np.int64), gt_i, 10)
+    assert abs(r_gpu - r_cpu) <= 1e-3, (r_gpu, r_cpu)  # recall@10 identical within 0.1 pp
+
+
+def test_f32_queries_and_float_inputs():
+    """f32 host inputs (the reference's documented dtype) take the cast path."""
+    n, nq, C, B = 8000, 300, 8, 2
+    X, Q, layers, pred = _synthetic(n, nq, C, steps=40)
+    li = _index(layers, C)
+    d16, i16, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=B)
+    li2 = _index(layers, C)
+    d32, i32, _ = li2.search(None, Q.astype(np.float32), X.astype(np.float32), Q.astype(np.float32), pred, [C],
+                             n_buckets=B)
+    assert np.array_equal(i16, i32)
+    np.testing.assert_array_equal(d16, d32)
+
+
+def test_full_probe_is_exact_brute_force():
+    """B == C scans every bucket: result must equal exact k-NN (size-independent property)."""
+    n, nq, C = 30_000, 400, 12
+    X, Q, layers, pred = _synthetic(n, nq, C, steps=40)
+    li = _index(layers, C)
+    d, i, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=C, k=10)
+    gt_d, gt_i = orc.brute_force(Q, X)
+    assert orc.get_recall(i.astype(np.int64), gt_i, 10) > 0.9995
+    np.testing.assert_allclose(d, gt_d.astype(np.float64), rtol=1e-3, atol=2e-6)
+    assert (np.diff(d, axis=1) >= 0).all(), "distances must be ascending"
+
+
+def test_pandas_dataframes_and_labels():
+    """The reference's calling convention: DataFrames with a 1-based index, two distinct frames."""
+    import pandas as pd
+
+    n, nq, C, B = 5000, 128, 6, 2
+    X, Q, layers, pred = _synthetic(n, nq, C, steps=40)
+    ids = np.arange(1, n + 1)
+    df_nav = pd.DataFrame(X, index=pd.Index(ids))
+    df_search = pd.DataFrame(X, index=pd.Index(ids))
+    cols_before = list(df_nav.columns)
+    li = _index(layers, C)
+    d, i, _ = li.search(df_nav, Q, df_search, Q, pred, [C], n_buckets=B, k=10)
+    assert list(df_nav.columns) == cols_before  # not mutated
+    exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=10)
+    same = (li.last_bucket_order.cpu().numpy() == exp_order[:, :, 0]).all(axis=1)
+    assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what="pandas")
+    assert i.min() >= 1 and i.max() <= n
+
+
+def test_errors():
+    n, nq, C = 2000, 16, 5
+    X, Q, layers, pred = _synthetic(n, nq, C, steps=20)
+    li = _index(layers, C)
+    with pytest.raises(ValueError):
+        li.search(None, Q, X, Q, pred, [C], n_buckets=C + 1)
+    with pytest.raises(AssertionError):
+        li.search(None, Q, X, Q[:, :64], pred, [C], n_buckets=1)
+    with pytest.raises(AssertionError):
+        li.search(None, Q, X, Q, pred, [C], n_buckets=2, k=25)
+    d, i, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=1, k=3)
+    assert d.shape == (nq, 10)  # `k` is not forwarded when n_buckets == 1 (LearnedIndex.py:111-117)
+    d, i, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=3, k=20)
+    assert d.shape == (nq, 20)
