@@ -78,6 +78,8 @@ class NeuralNetwork:
         ``Linear``/``ReLU``, model.py:94) or from anything exposing ``state_dict()``."""
         if isinstance(nn, cls):
             return nn
+        if isinstance(nn, (list, tuple)):  # raw [(W, b), ...]
+            return cls(nn, device=device)
         module = getattr(nn, "model", nn)
         sd = module.state_dict()
         idx = sorted({int(k.split(".")[-2]) for k in sd if k.endswith(".weight")})
