@@ -131,9 +131,10 @@ class LearnedIndex:
 
     # ------------------------------------------------------------------ search ------
     def search_device(self, qn: torch.Tensor, qs: torch.Tensor, n_categories: List[int], n_buckets: int, k: int,
-                      events=None):
+                      events=None, out=None):
         """Everything between the H2D and D2H copies.  ``qn`` / ``qs``: device matrices
-        (fp16 or f32).  Returns device tensors (dists f64[nq,k'], nns int32-bits[nq,k'])."""
+        (fp16 or f32).  Returns device tensors (dists f64[nq,k'], nns int32-bits[nq,k']);
+        ``out=(dists, nns)`` supplies them (e.g. views into an all-gather send buffer)."""
         L = _native.lib()
         layout = self._layout
         assert layout is not None, "call prepare()/attach_layout() first"
@@ -154,8 +155,13 @@ class LearnedIndex:
         self.last_bucket_order, self.last_probs = order, probs
         mark(1)
 
-        dists = torch.empty((nq, k_out), dtype=torch.float64, device=dev)
-        nns = torch.empty((nq, k_out), dtype=torch.int32, device=dev)
+        if out is not None:
+            dists, nns = out
+            assert dists.shape == (nq, k_out) and dists.dtype == torch.float64 and dists.is_contiguous()
+            assert nns.shape == (nq, k_out) and nns.dtype == torch.int32 and nns.is_contiguous()
+        else:
+            dists = torch.empty((nq, k_out), dtype=torch.float64, device=dev)
+            nns = torch.empty((nq, k_out), dtype=torch.int32, device=dev)
         if nq == 0:
             for i in (2, 3, 4):
                 mark(i)

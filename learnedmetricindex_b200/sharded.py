@@ -1,0 +1,154 @@
+"""Bucket-sharded search over the GPUs of one box (one process per GPU).
+
+The reference is single-process; this is the multi-GPU form BASELINE.json's
+north_star asks for.  Buckets are independent units, so whole buckets are assigned to
+ranks; MLP weights and the query batch are replicated; every rank runs the single-GPU
+path (``LearnedIndex.search_device``) over the buckets it owns -- a probed bucket that
+lives elsewhere is an empty bucket locally and yields the reference's "no candidate"
+filler (id 0, +inf; LearnedIndex.py:340-341) -- and the only exchange step is ONE
+all-gather of the per-rank ``[nq, k]`` results (``nq*k*12`` bytes per rank; 1.2 MB at
+10k x 10) over NCCL/NVLink followed by ``lmi_merge_ranks`` on every rank.
+
+The all-gather buffer is packed ``[dists f64 | nns u32]`` per rank and the local merge
+kernel writes straight into this rank's send slot, so there is no staging copy.
+
+Host-side logic (partitioning, buffer packing, gather, merge order) is backend-agnostic:
+``tests/test_sharded_gloo.py`` runs it with world_size 2 over gloo on CPU, injecting a
+numpy merge in place of the CUDA kernel.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def partition_buckets(sizes: Sequence[int], world: int, weights: Optional[Sequence[float]] = None) -> List[List[int]]:
+    """Longest-processing-time greedy assignment of whole buckets to ``world`` ranks.
+
+    ``sizes[b]`` = rows of bucket b; ``weights[b]`` (optional) = expected probes of bucket b,
+    so the balanced quantity is scan work ``s_b * w_b`` (HBM bytes when all weights are 1).
+    Deterministic: ties go to the lower bucket id / lower rank, so every rank derives the
+    same map without communicating."""
+    sizes = np.asarray(sizes, dtype=np.float64)
+    cost = sizes if weights is None else sizes * np.asarray(weights, dtype=np.float64)
+    order = sorted(range(len(sizes)), key=lambda b: (-cost[b], b))
+    load = [0.0] * world
+    mine: List[List[int]] = [[] for _ in range(world)]
+    for b in order:
+        r = min(range(world), key=lambda w: (load[w], w))
+        mine[r].append(b)
+        load[r] += float(cost[b])
+    return [sorted(m) for m in mine]
+
+
+def owner_of_bucket(parts: List[List[int]], n_buckets: int) -> np.ndarray:
+    own = np.full(n_buckets, -1, dtype=np.int64)
+    for r, bs in enumerate(parts):
+        own[bs] = r
+    assert (own >= 0).all()
+    return own
+
+
+class GatherBuffers:
+    """Packed all-gather buffers: per rank ``[nq*k f64][nq*k u32]`` padded to 16 bytes."""
+
+    def __init__(self, nq: int, k: int, world: int, rank: int, device):
+        self.nq, self.k, self.world, self.rank = nq, k, world, rank
+        self.bytes_d = nq * k * 8
+        self.bytes_i = nq * k * 4
+        self.per_rank = -(-(self.bytes_d + self.bytes_i) // 16) * 16
+        self.send = torch.zeros(self.per_rank, dtype=torch.uint8, device=device)
+        self.recv = torch.zeros(self.per_rank * world, dtype=torch.uint8, device=device)
+
+    def local_views(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        d = self.send[: self.bytes_d].view(torch.float64).view(self.nq, self.k)
+        i = self.send[self.bytes_d : self.bytes_d + self.bytes_i].view(torch.int32).view(self.nq, self.k)
+        return d, i
+
+    def rank_views(self, w: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        base = w * self.per_rank
+        d = self.recv[base : base + self.bytes_d].view(torch.float64).view(self.nq, self.k)
+        i = self.recv[base + self.bytes_d : base + self.bytes_d + self.bytes_i].view(torch.int32).view(self.nq, self.k)
+        return d, i
+
+    @property
+    def stride_d(self) -> int:  # elements between consecutive ranks' dist blocks
+        return self.per_rank // 8
+
+    @property
+    def stride_i(self) -> int:
+        return self.per_rank // 4
+
+
+def merge_ranks_device(buf: GatherBuffers, out_d: torch.Tensor, out_i: torch.Tensor) -> None:
+    """``lmi_merge_ranks`` over the gathered buffer (CUDA)."""
+    from . import _native
+
+    L = _native.lib()
+    base = buf.recv.data_ptr()
+    _native.check(L.lmi_merge_ranks(base, base + buf.bytes_d, buf.stride_d, buf.stride_i, buf.world, buf.nq, buf.k,
+                                    out_d.data_ptr(), out_i.data_ptr(), torch.cuda.current_stream().cuda_stream),
+                  "lmi_merge_ranks")
+
+
+def gather_and_merge(buf: GatherBuffers, group=None,
+                     merge_fn: Callable[[GatherBuffers, torch.Tensor, torch.Tensor], None] = merge_ranks_device):
+    """The exchange step: all-gather the packed per-rank results, then k-way merge."""
+    dist.all_gather_into_tensor(buf.recv, buf.send, group=group)
+    out_d = torch.empty((buf.nq, buf.k), dtype=torch.float64, device=buf.send.device)
+    out_i = torch.empty((buf.nq, buf.k), dtype=torch.int32, device=buf.send.device)
+    merge_fn(buf, out_d, out_i)
+    return out_d, out_i
+
+
+class ShardedLearnedIndex:
+    """``LearnedIndex`` whose buckets are spread over the ranks of ``group``.
+
+    ``local`` is this rank's ``LearnedIndex`` with a layout holding only the buckets it
+    owns (``DeviceBucketLayout.restrict_to_buckets`` or a layout built from the local rows).
+    """
+
+    def __init__(self, local, group=None):
+        self.local = local
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self._bufs = {}
+
+    def _buffers(self, nq: int, k: int, device) -> GatherBuffers:
+        key = (nq, k)
+        if key not in self._bufs:
+            self._bufs[key] = GatherBuffers(nq, k, self.world, self.rank, device)
+        return self._bufs[key]
+
+    def search_device(self, qn, qs, n_categories, n_buckets: int, k: int, events=None):
+        from .LearnedIndex import PER_BUCKET_K
+
+        nq = qs.shape[0]
+        k_out = PER_BUCKET_K if int(n_buckets) == 1 else int(k)
+        buf = self._buffers(nq, k_out, qs.device)
+        self.local.search_device(qn, qs, n_categories, n_buckets, k, events=events, out=buf.local_views())
+        return gather_and_merge(buf, self.group)
+
+    def search(self, data_navigation, queries_navigation, data_search, queries_search, data_prediction,
+               n_categories, n_buckets: int = 1, k: int = 10):
+        """Same signature as ``LearnedIndex.search``; the layout must already be attached
+        (each rank holds only its shard, so the host frames are not used)."""
+        import time
+        from collections import defaultdict
+
+        from .model import to_device_matrix
+
+        t0 = time.time()
+        dev = self.local.device
+        qn = to_device_matrix(queries_navigation, dev)
+        qs = qn if queries_search is queries_navigation else to_device_matrix(queries_search, dev)
+        d, i = self.search_device(qn, qs, list(n_categories), n_buckets, k)
+        dists = d.cpu().numpy()
+        nns = i.cpu().numpy().view(np.uint32)
+        times = defaultdict(float)
+        times["search"] = time.time() - t0
+        return dists, nns, times

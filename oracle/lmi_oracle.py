@@ -247,6 +247,24 @@ class BucketMajor:
         self.ids = np.asarray(ids)[perm]
         self.n_levels = n_levels
 
+    @classmethod
+    def from_grouped(cls, vectors: np.ndarray, offsets: np.ndarray, ids: np.ndarray, paths=None) -> "BucketMajor":
+        """Adopt rows that are ALREADY grouped by bucket (ascending bucket id, original
+        order inside a bucket) -- the same grouping ``__init__`` derives -- without the
+        extra full copy.  ``offsets`` int64[C+1]; buckets without rows are not listed as
+        groups, exactly as ``groupby`` omits absent keys (:350)."""
+        self = cls.__new__(cls)
+        offsets = np.asarray(offsets, dtype=np.int64)
+        sizes = np.diff(offsets)
+        present = np.flatnonzero(sizes > 0)
+        all_paths = paths if paths is not None else [(int(b),) for b in range(len(sizes))]
+        self.paths = [tuple(all_paths[b]) for b in present]
+        self.offsets = np.concatenate((offsets[present], [offsets[-1]])).astype(np.int64)
+        self.vectors = vectors
+        self.ids = np.asarray(ids)
+        self.n_levels = len(self.paths[0]) if self.paths else 1
+        return self
+
 
 def search_round(
     layout: BucketMajor, queries_search: np.ndarray, bucket_path: np.ndarray, k: int = PER_BUCKET_K
@@ -318,6 +336,16 @@ def search(
             assert out_d.shape == out_i.shape == (queries_search.shape[0], k)  # :142-146
     times["search"] = time.time() - t_start
     return out_d, out_i, dict(times), order
+
+
+def merge_ranks(dists_per_rank: Sequence[np.ndarray], nns_per_rank: Sequence[np.ndarray], k: int):
+    """Cross-GPU merge (no reference counterpart; the reference is single-process): the
+    same stable rule as ``merge_rounds`` applied over ranks in rank order -- the k smallest
+    per query, ties keeping the lower rank, then the lower position."""
+    d = np.hstack(list(dists_per_rank))
+    i = np.hstack(list(nns_per_rank))
+    keep = d.argsort(kind="stable", axis=1)[:, :k]
+    return np.take_along_axis(d, keep, axis=1), np.take_along_axis(i, keep, axis=1)
 
 
 # --------------------------------------------------------------------------- #
