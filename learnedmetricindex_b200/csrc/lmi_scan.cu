@@ -34,6 +34,7 @@ constexpr int SCAN_MAX_D = 768;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t TMEM_ACC_COL = SCAN_MAX_D / 2;  // A: columns [0,384); accumulators: [384,448), [448,512)
 constexpr int TOPK = LMI_PER_BUCKET_K;
+constexpr int SCAN_EPI_COLS = 16;     // accumulator columns the epilogue pulls from TMEM per step
 constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
 
 struct ScanBarriers {
@@ -229,29 +230,33 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 const uint32_t buf = tcount & 1;
                 ptx::mbar_wait(&bars->acc_full[buf], (tcount >> 1) & 1);
                 ptx::tc_fence_after();
-                uint32_t v0[32], v1[32];
                 const uint32_t taddr = tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N;
-                ptx::tmem_ld32(taddr, v0);
-                ptx::tmem_ld32(taddr + 32, v1);
-                ptx::tmem_ld_wait();
-                ptx::tc_fence_before();
-                ptx::mbar_arrive(&bars->acc_empty[buf]);
-
                 const int base_row = row0 + t * SCAN_N;
                 const int live = nrows - t * SCAN_N;  // rows of this tile that belong to the range
-                if (live >= SCAN_N) {
+                // Rolled on purpose: the whole top-10 bookkeeping must stay resident in the
+                // instruction cache (a fully unrolled 64-column version is > 100 KB of SASS and
+                // ran fetch-bound).  16 columns at a time: one max-reduction rejects the chunk
+                // unless some lane of the warp holds a candidate.
+#pragma unroll 1
+                for (int c = 0; c < SCAN_N; c += SCAN_EPI_COLS) {
+                    uint32_t v[SCAN_EPI_COLS];
+                    ptx::tmem_ld16(taddr + c, v);
+                    ptx::tmem_ld_wait();
+                    float m = __uint_as_float(v[0]);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) tk.offer(__uint_as_float(v0[j]), base_row + j);
+                    for (int j = 1; j < SCAN_EPI_COLS; ++j) m = fmaxf(m, __uint_as_float(v[j]));
+                    const int lim = live - c;  // columns of this chunk inside the range
+                    const bool cand = lim > 0 && m > tk.s[TOPK - 1];
+                    if (__any_sync(0xffffffffu, cand)) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) tk.offer(__uint_as_float(v1[j]), base_row + 32 + j);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (j < live) tk.offer(__uint_as_float(v0[j]), base_row + j);
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (32 + j < live) tk.offer(__uint_as_float(v1[j]), base_row + 32 + j);
+                        for (int j = 0; j < SCAN_EPI_COLS; ++j) {
+                            const float f = __uint_as_float(v[j]);
+                            if (j < lim && f > tk.s[TOPK - 1]) tk.insert(f, base_row + c + j);
+                        }
+                    }
                 }
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(&bars->acc_empty[buf]);
             }
             if (valid) store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * rmax + range_idx) * TOPK);
         }
