@@ -27,8 +27,10 @@ namespace lmi {
 constexpr int SCAN_M = 128;        // queries per item (TMEM lanes)
 constexpr int SCAN_N = 64;         // bucket rows per MMA tile
 constexpr int SCAN_KBLK = 64;      // fp16 per 128-byte shared-memory row
-constexpr int SCAN_STAGE_BYTES = SCAN_N * 128;
-constexpr int SCAN_STAGES = 24;
+constexpr int SCAN_BOX_BYTES = SCAN_N * 128;  // one TMA box: 64 rows x 64 fp16
+constexpr int SCAN_BOXES = 4;                  // boxes (k-blocks) per pipeline stage: one barrier round-trip per 16 MMAs
+constexpr int SCAN_STAGE_BYTES = SCAN_BOXES * SCAN_BOX_BYTES;
+constexpr int SCAN_STAGES = 6;
 constexpr int SCAN_THREADS = 192;
 constexpr int SCAN_MAX_D = 768;
 constexpr uint32_t TMEM_COLS = 512;
@@ -127,66 +129,80 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
 
     if (warp == 4) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            const uint64_t policy = ptx::policy_evict_normal();
-            uint32_t stage = 0, phase = 0;
-            for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-                const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
-                const int row0 = w0.x, nrows = w0.y;
-                const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
-                for (int t = 0; t < ntiles; ++t) {
-                    for (int kb = 0; kb < KB; ++kb) {
-                        ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
-                        ptx::mbar_arrive_expect_tx(&bars->full[stage], SCAN_STAGE_BYTES);
-                        ptx::tma_load_2d(stages + (size_t)stage * SCAN_STAGE_BYTES, &tmap, kb * SCAN_KBLK,
-                                         row0 + t * SCAN_N, &bars->full[stage], policy);
-                        if (++stage == SCAN_STAGES) {
-                            stage = 0;
-                            phase ^= 1;
-                        }
+        // The whole warp walks the loop (warp-uniform control flow); one elected lane issues, so
+        // ptxas emits the TMA / mbarrier instructions straight, without a per-thread waterfall loop.
+        const uint64_t policy = ptx::policy_evict_normal();
+        const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;  // stages per 64-row tile
+        uint32_t stage = 0, phase = 0;
+        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+            const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+            const int row0 = w0.x, nrows = w0.y;
+            const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+            for (int t = 0; t < ntiles; ++t) {
+                for (int s = 0; s < SPT; ++s) {
+                    const int kb0 = s * SCAN_BOXES;
+                    const int nb = min(SCAN_BOXES, KB - kb0);
+                    ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
+                    if (ptx::elect_one()) {
+                        uint8_t* dst = stages + (size_t)stage * SCAN_STAGE_BYTES;
+                        ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
+                        for (int b = 0; b < nb; ++b)
+                            ptx::tma_load_2d(dst + b * SCAN_BOX_BYTES, &tmap, (kb0 + b) * SCAN_KBLK, row0 + t * SCAN_N,
+                                             &bars->full[stage], policy);
+                    }
+                    __syncwarp();
+                    if (++stage == SCAN_STAGES) {
+                        stage = 0;
+                        phase ^= 1;
                     }
                 }
             }
         }
-        __syncwarp();
     } else if (warp == 5) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
-            uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0;
-            for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-                const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
-                const int nrows = w0.y;
-                const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
-                ptx::mbar_wait(&bars->q_ready, item_parity);
-                item_parity ^= 1;
+        constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
+        const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;
+        const uint64_t desc0 = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(stages));
+        uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0;
+        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+            const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+            const int nrows = w0.y;
+            const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+            ptx::mbar_wait(&bars->q_ready, item_parity);
+            item_parity ^= 1;
+            ptx::tc_fence_after();
+            for (int t = 0; t < ntiles; ++t, ++tcount) {
+                const uint32_t buf = tcount & 1;
+                ptx::mbar_wait(&bars->acc_empty[buf], ((tcount >> 1) & 1) ^ 1);
                 ptx::tc_fence_after();
-                for (int t = 0; t < ntiles; ++t, ++tcount) {
-                    const uint32_t buf = tcount & 1;
-                    ptx::mbar_wait(&bars->acc_empty[buf], ((tcount >> 1) & 1) ^ 1);
+                const uint32_t d_tmem = tmem + TMEM_ACC_COL + buf * SCAN_N;
+                for (int s = 0; s < SPT; ++s) {
+                    const int kb0 = s * SCAN_BOXES;
+                    const int nb = min(SCAN_BOXES, KB - kb0);
+                    ptx::mbar_wait(&bars->full[stage], phase);
                     ptx::tc_fence_after();
-                    const uint32_t d_tmem = tmem + TMEM_ACC_COL + buf * SCAN_N;
-                    for (int kb = 0; kb < KB; ++kb) {
-                        ptx::mbar_wait(&bars->full[stage], phase);
-                        ptx::tc_fence_after();
-                        const uint32_t b_base = ptx::smem_u32(stages + (size_t)stage * SCAN_STAGE_BYTES);
+                    if (ptx::elect_one()) {
+                        // descriptor start-address field counts 16-byte units: stage and box offsets add linearly
+                        const uint64_t sdesc = desc0 + (uint64_t)((stage * SCAN_STAGE_BYTES) >> 4);
+                        for (int b = 0; b < nb; ++b) {
 #pragma unroll
-                        for (int k = 0; k < SCAN_KBLK / 16; ++k) {
-                            const uint64_t b_desc = ptx::umma_desc_sw128_kmajor(b_base + k * 32);
-                            const uint32_t a_tmem = tmem + kb * (SCAN_KBLK / 2) + k * 8;
-                            ptx::mma_f16_ts(d_tmem, a_tmem, b_desc, idesc, (kb | k) != 0 ? 1u : 0u);
+                            for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                                const uint64_t b_desc = sdesc + (uint64_t)((b * SCAN_BOX_BYTES + k * 32) >> 4);
+                                const uint32_t a_tmem = tmem + (kb0 + b) * (SCAN_KBLK / 2) + k * 8;
+                                ptx::mma_f16_ts(d_tmem, a_tmem, b_desc, idesc, (s | b | k) != 0 ? 1u : 0u);
+                            }
                         }
                         ptx::mma_commit(&bars->empty[stage]);
-                        if (++stage == SCAN_STAGES) {
-                            stage = 0;
-                            phase ^= 1;
-                        }
+                        if (s == SPT - 1) ptx::mma_commit(&bars->acc_full[buf]);
                     }
-                    ptx::mma_commit(&bars->acc_full[buf]);
+                    __syncwarp();
+                    if (++stage == SCAN_STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
                 }
             }
         }
-        __syncwarp();
     } else {
         // ===================== epilogue warps (thread == query row) =====================
         const int row = warp * 32 + lane;
