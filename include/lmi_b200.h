@@ -46,7 +46,7 @@
 extern "C" {
 #endif
 
-#define LMI_B200_ABI_VERSION 1
+#define LMI_B200_ABI_VERSION 2
 
 #define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
 #define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
@@ -54,6 +54,7 @@ extern "C" {
 
 #define LMI_PER_BUCKET_K 10 /* `k` is not forwarded to _search_single_bucket (LearnedIndex.py:111-117,:334) */
 #define LMI_ITEM_WORDS 8    /* int32 words per scan work item, see lmi_invert */
+#define LMI_LISTS_PER_ITEM 2 /* partial top-10 lists a scan work item writes per query (one per column half) */
 
 int lmi_version(void);
 const char *lmi_error_string(int code);
@@ -98,16 +99,18 @@ int64_t lmi_invert_workspace_ints(int nq, int B, int C);
  *   range_len                  in   rows per work item (multiple of 64)
  *   counts       int32[C]      out  m_b = pairs probing bucket b
  *   offsets      int32[C+1]    out  exclusive scan of counts
+ *   bucket_lists int32[C]      out  partial lists the scan writes per (query, bucket b) pair
+ *                                   (= ranges of b x LMI_LISTS_PER_ITEM; 0 for an unprobed bucket)
  *   pair_list    int32[nq*B]   out  flat pair index per sorted slot
  *   slot_of_pair int32[nq*B]   out  inverse permutation (-1 for ignored pairs)
- *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, range_idx, bucket, 0, 0}
+ *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, first list, bucket, 0, 0}
  *   n_items      int32[1]      out
  *   workspace    int32[lmi_invert_workspace_ints(nq,B,C)]  scratch
  */
 int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t *bucket_off,
-               int range_len, int32_t *counts, int32_t *offsets, int32_t *pair_list,
-               int32_t *slot_of_pair, int32_t *items, int32_t *n_items, int64_t max_items,
-               int32_t *workspace, void *stream);
+               int range_len, int32_t *counts, int32_t *offsets, int32_t *bucket_lists,
+               int32_t *pair_list, int32_t *slot_of_pair, int32_t *items, int32_t *n_items,
+               int64_t max_items, int32_t *workspace, void *stream);
 
 /* ---- candidate scan + fused per-range top-10 ---------------------------------- */
 
@@ -116,19 +119,22 @@ int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t 
  * 10 largest per query.  The full similarity matrix is never written.
  *   X         fp16[n,d] bucket-major, 16-byte aligned, d % 64 == 0, 64 <= d <= 768
  *   Q         fp16[nq,d]
- *   part_sim  f32 [nq*B, rmax, 10] out  descending; -inf where fewer than 10 rows
- *   part_row  i32 [nq*B, rmax, 10] out  row index into X; -1 where empty
+ *   lmax      lists allocated per (query, probe) pair: >= max_b bucket_lists[b]
+ *   part_sim  f32 [nq*B, lmax, 10] out  descending; -inf where fewer than 10 rows
+ *   part_row  i32 [nq*B, lmax, 10] out  row index into X; -1 where empty
+ * An item writes lists {first list, first list + 1} of each of its queries.
  * impl: 0 = tcgen05/TMA kernel (product path), 1 = plain CUDA-core verification
  * kernel (tests only; any d).
  */
 int lmi_scan_topk(const void *X, int64_t n, int d, const void *Q, int nq, int B,
                   const int32_t *pair_list, const int32_t *items, const int32_t *n_items,
-                  int64_t max_items, int rmax, float *part_sim, int32_t *part_row,
+                  int64_t max_items, int lmax, float *part_sim, int32_t *part_row,
                   int impl, void *stream);
 
 /* ---- merge ------------------------------------------------------------------- */
 
-/* Per query: reduce each probe's per-range lists to that bucket's top-10, turn
+/* Per query: reduce each probe's partial lists (bucket_lists[b] of them, ties between
+ * equal similarities go to the lower row) to that bucket's top-10, turn
  * similarities into distances 1 - sim (f32), map rows to ids, pad as the reference
  * does (undersized bucket: last id of the bucket, 1 + FLT_MAX; empty or unknown
  * bucket: id 0, +inf), then keep the k_out smallest over all probes -- ties keep the
@@ -139,7 +145,7 @@ int lmi_scan_topk(const void *X, int64_t n, int d, const void *Q, int nq, int B,
  */
 int lmi_merge_topk(const float *part_sim, const int32_t *part_row, const int32_t *slot_of_pair,
                    const int32_t *bucket_order, const int64_t *bucket_off, const uint32_t *ids,
-                   int nq, int B, int C, int range_len, int rmax, int k_out,
+                   const int32_t *bucket_lists, int nq, int B, int C, int lmax, int k_out,
                    double *dists, uint32_t *nns, void *stream);
 
 /* Cross-GPU merge after the all-gather of the per-rank results: rank w's ascending

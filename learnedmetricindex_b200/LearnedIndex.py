@@ -29,7 +29,8 @@ from .model import NeuralNetwork, to_device_matrix
 
 EMPTY_VALUE = -1  # search/li/PriorityQueue.py:4
 PER_BUCKET_K = 10  # `k` is not forwarded to _search_single_bucket (LearnedIndex.py:111-117, :334)
-MAX_RANGES = 32  # lists per (query, probe) the merge kernel walks with one lane each
+MAX_RANGES = 32  # row ranges a bucket is cut into at most
+LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
 
 
@@ -176,7 +177,9 @@ class LearnedIndex:
         range_len, rmax = plan_scan(nq, B, C, layout.n, layout.max_bucket, self._n_sms)
         P = nq * B
         max_items = int(L.lmi_max_items(nq, B, C, rmax))
+        lmax = rmax * LISTS_PER_ITEM
         counts = torch.empty(C, dtype=torch.int32, device=dev)
+        bucket_lists = torch.empty(C, dtype=torch.int32, device=dev)
         offsets = torch.empty(C + 1, dtype=torch.int32, device=dev)
         pair_list = torch.empty(P, dtype=torch.int32, device=dev)
         slot_of_pair = torch.empty(P, dtype=torch.int32, device=dev)
@@ -184,22 +187,23 @@ class LearnedIndex:
         n_items = torch.zeros(1, dtype=torch.int32, device=dev)
         work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
         _native.check(L.lmi_invert(order.data_ptr(), nq, B, C, layout.bucket_off.data_ptr(), range_len,
-                                   counts.data_ptr(), offsets.data_ptr(), pair_list.data_ptr(),
+                                   counts.data_ptr(), offsets.data_ptr(), bucket_lists.data_ptr(), pair_list.data_ptr(),
                                    slot_of_pair.data_ptr(), items.data_ptr(), n_items.data_ptr(), max_items,
                                    work.data_ptr(), _stream_ptr()), "lmi_invert")
         mark(2)
 
-        part_sim = torch.empty(P * rmax * PER_BUCKET_K, dtype=torch.float32, device=dev)
-        part_row = torch.empty(P * rmax * PER_BUCKET_K, dtype=torch.int32, device=dev)
+        part_sim = torch.empty(P * lmax * PER_BUCKET_K, dtype=torch.float32, device=dev)
+        part_row = torch.empty(P * lmax * PER_BUCKET_K, dtype=torch.int32, device=dev)
         if layout.n > 0:
             _native.check(L.lmi_scan_topk(layout.vectors.data_ptr(), layout.n, layout.d, q16.data_ptr(), nq, B,
                                           pair_list.data_ptr(), items.data_ptr(), n_items.data_ptr(), max_items,
-                                          rmax, part_sim.data_ptr(), part_row.data_ptr(), self.scan_impl,
+                                          lmax, part_sim.data_ptr(), part_row.data_ptr(), self.scan_impl,
                                           _stream_ptr()), "lmi_scan_topk")
         mark(3)
         _native.check(L.lmi_merge_topk(part_sim.data_ptr(), part_row.data_ptr(), slot_of_pair.data_ptr(),
-                                       order.data_ptr(), layout.bucket_off.data_ptr(), layout.ids.data_ptr(), nq, B,
-                                       C, range_len, rmax, k_out, dists.data_ptr(), nns.data_ptr(), _stream_ptr()),
+                                       order.data_ptr(), layout.bucket_off.data_ptr(), layout.ids.data_ptr(),
+                                       bucket_lists.data_ptr(), nq, B, C, lmax, k_out, dists.data_ptr(),
+                                       nns.data_ptr(), _stream_ptr()),
                       "lmi_merge_topk")
         mark(4)
         self.last_plan = dict(range_len=range_len, rmax=rmax, max_items=max_items, n_items=n_items,

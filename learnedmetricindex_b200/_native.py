@@ -63,11 +63,11 @@ _SIGNATURES = {
     "lmi_cast_f16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "lmi_max_items": (c_int64, [c_int, c_int, c_int, c_int]),
     "lmi_invert_workspace_ints": (c_int64, [c_int, c_int, c_int]),
-    "lmi_invert": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+    "lmi_invert": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                            c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "lmi_scan_topk": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
                               c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p]),
-    "lmi_merge_topk": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+    "lmi_merge_topk": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "lmi_merge_ranks": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p]),

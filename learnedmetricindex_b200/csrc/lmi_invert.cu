@@ -80,8 +80,8 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* warp_tot, int& t
 // pass 2 (one block): column scan of hist over chunks, bucket offsets, work items.
 __global__ void __launch_bounds__(1024)
 invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __restrict__ bucket_off, int range_len,
-                   int32_t* __restrict__ counts, int32_t* __restrict__ offsets, int32_t* __restrict__ items,
-                   int32_t* __restrict__ n_items, int64_t max_items) {
+                   int32_t* __restrict__ counts, int32_t* __restrict__ offsets, int32_t* __restrict__ bucket_lists,
+                   int32_t* __restrict__ items, int32_t* __restrict__ n_items, int64_t max_items) {
     __shared__ int warp_tot[33];
     __shared__ int carry_pairs, carry_items;
     if (threadIdx.x == 0) {
@@ -114,6 +114,7 @@ invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __re
                 nt = (m + SCAN_M_TILE - 1) / SCAN_M_TILE;
             }
         }
+        if (c < C) bucket_lists[c] = nr * LMI_LISTS_PER_ITEM;
         int tot_items;
         const int ibase = block_exclusive_scan(nr * nt, warp_tot, tot_items) + carry_items;
         for (int r = 0; r < nr; ++r) {
@@ -124,7 +125,7 @@ invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __re
                 if (idx >= max_items) continue;
                 int4* dst = reinterpret_cast<int4*>(items + idx * LMI_ITEM_WORDS);
                 dst[0] = make_int4((int)row0, nrows, off + t * SCAN_M_TILE, min(SCAN_M_TILE, m - t * SCAN_M_TILE));
-                dst[1] = make_int4(r, c, 0, 0);
+                dst[1] = make_int4(r * LMI_LISTS_PER_ITEM, c, 0, 0);
             }
         }
         __syncthreads();
@@ -193,11 +194,11 @@ extern "C" int64_t lmi_invert_workspace_ints(int nq, int B, int C) {
 }
 
 extern "C" int lmi_invert(const int32_t* bucket_order, int nq, int B, int C, const int64_t* bucket_off,
-                          int range_len, int32_t* counts, int32_t* offsets, int32_t* pair_list,
-                          int32_t* slot_of_pair, int32_t* items, int32_t* n_items, int64_t max_items,
-                          int32_t* workspace, void* stream) {
-    if (!bucket_order || !bucket_off || !counts || !offsets || !pair_list || !slot_of_pair || !items || !n_items ||
-        !workspace)
+                          int range_len, int32_t* counts, int32_t* offsets, int32_t* bucket_lists,
+                          int32_t* pair_list, int32_t* slot_of_pair, int32_t* items, int32_t* n_items,
+                          int64_t max_items, int32_t* workspace, void* stream) {
+    if (!bucket_order || !bucket_off || !counts || !offsets || !bucket_lists || !pair_list || !slot_of_pair ||
+        !items || !n_items || !workspace)
         return LMI_E_BADARG;
     if (nq <= 0 || B <= 0 || C <= 0 || range_len <= 0 || range_len % 64 != 0 || max_items <= 0) return LMI_E_BADARG;
     const int64_t P = (int64_t)nq * B;
@@ -207,8 +208,8 @@ extern "C" int lmi_invert(const int32_t* bucket_order, int nq, int B, int C, con
     const int64_t chunk = lmi::inv_chunk_len(P, G);
     const int blocks = (G + lmi::INV_WARPS_PER_BLOCK - 1) / lmi::INV_WARPS_PER_BLOCK;
     lmi::invert_hist_kernel<<<blocks, lmi::INV_WARPS_PER_BLOCK * 32, 0, st>>>(bucket_order, P, C, G, chunk, workspace);
-    lmi::invert_scan_kernel<<<1, 1024, 0, st>>>(workspace, C, G, bucket_off, range_len, counts, offsets, items,
-                                                n_items, max_items);
+    lmi::invert_scan_kernel<<<1, 1024, 0, st>>>(workspace, C, G, bucket_off, range_len, counts, offsets,
+                                                bucket_lists, items, n_items, max_items);
     lmi::invert_scatter_kernel<<<blocks, lmi::INV_WARPS_PER_BLOCK * 32, 0, st>>>(bucket_order, P, C, G, chunk,
                                                                                  workspace, offsets, pair_list,
                                                                                  slot_of_pair);

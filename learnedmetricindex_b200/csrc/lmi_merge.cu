@@ -32,12 +32,14 @@ __device__ __forceinline__ void warp_argmin(float& d, int& e) {
     }
 }
 
+constexpr int MERGE_LPL = 8;  // lists per lane: up to 256 partial lists per (query, probe)
+
 // One warp per query.  Shared memory per warp: B*10 (dist f32, id u32) pairs.
 __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int32_t* __restrict__ part_row,
                                   const int32_t* __restrict__ slot_of_pair, const int32_t* __restrict__ order,
-                                  const int64_t* __restrict__ bucket_off, const uint32_t* __restrict__ ids, int nq,
-                                  int B, int C, int range_len, int rmax, int k_out, double* __restrict__ dists,
-                                  uint32_t* __restrict__ nns) {
+                                  const int64_t* __restrict__ bucket_off, const uint32_t* __restrict__ ids,
+                                  const int32_t* __restrict__ bucket_lists, int nq, int B, int C, int lmax,
+                                  int k_out, double* __restrict__ dists, uint32_t* __restrict__ nns) {
     extern __shared__ float sm[];
     const int warps = blockDim.x >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -64,27 +66,42 @@ __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int3
             }
             continue;
         }
-        const int nr = (int)((hi - lo + range_len - 1) / range_len);
+        const int nl = min(bucket_lists[b], lmax);
         const int slot = slot_of_pair[p];
-        // lane rr walks the (descending) list of range rr; nr <= 32 is enforced by the host
-        const size_t base = ((size_t)slot * rmax + lane) * MK;
-        int head = 0;
-        float hv = -INFINITY;
-        int hrow = -1;
-        if (lane < nr) {
-            hv = part_sim[base];
-            hrow = part_row[base];
+        // lane walks the (descending) lists lane, lane+32, ...; a taken head is replaced by the
+        // list's next entry
+        const size_t base = (size_t)slot * lmax * MK;
+        float hv[MERGE_LPL];
+        int hrow[MERGE_LPL], head[MERGE_LPL];
+#pragma unroll
+        for (int u = 0; u < MERGE_LPL; ++u) {
+            const int l = lane + 32 * u;
+            hv[u] = -INFINITY;
+            hrow[u] = -1;
+            head[u] = 0;
+            if (l < nl) {
+                hv[u] = part_sim[base + (size_t)l * MK];
+                hrow[u] = part_row[base + (size_t)l * MK];
+            }
         }
         const uint32_t last_id = ids[hi - 1];
         for (int t = 0; t < MK; ++t) {
-            // arg max by (similarity desc, range asc): encode as (−sim asc, lane asc)
-            float kd = (hrow >= 0) ? -hv : INFINITY;
-            int ke = lane;
-            warp_argmin(kd, ke);
-            const bool none = !(kd < INFINITY);
-            const int win = ke;
-            const float wv = __shfl_sync(0xffffffffu, hv, win);
-            const int wrow = __shfl_sync(0xffffffffu, hrow, win);
+            // arg max by (similarity desc, row asc): the lower row wins a tie, as in one pass
+            // over the bucket in row order
+            float kd = INFINITY;
+            int ke = 0x7fffffff, ku = 0;
+#pragma unroll
+            for (int u = 0; u < MERGE_LPL; ++u) {
+                if (hrow[u] >= 0 && key_less(-hv[u], hrow[u], kd, ke)) {
+                    kd = -hv[u];
+                    ke = hrow[u];
+                    ku = u;
+                }
+            }
+            float wd = kd;
+            int wrow = ke;
+            warp_argmin(wd, wrow);
+            const bool none = wrow == 0x7fffffff;
             if (lane == 0) {
                 if (none) {
                     // fewer than 10 objects: faiss pads with I = -1 / D = -FLT_MAX, the reference maps
@@ -92,17 +109,23 @@ __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int3
                     e_dist[r * MK + t] = 1.0f - (-FLT_MAX);
                     e_id[r * MK + t] = last_id;
                 } else {
-                    e_dist[r * MK + t] = 1.0f - wv;
+                    e_dist[r * MK + t] = 1.0f + wd;
                     e_id[r * MK + t] = ids[wrow];
                 }
             }
-            if (!none && lane == win) {
-                ++head;
-                if (head < MK) {
-                    hv = part_sim[base + head];
-                    hrow = part_row[base + head];
-                } else {
-                    hrow = -1;
+            if (!none && ke == wrow) {  // rows are unique across lists: exactly one lane owns the winner
+#pragma unroll
+                for (int u = 0; u < MERGE_LPL; ++u) {
+                    if (u == ku) {
+                        const int l = lane + 32 * u;
+                        ++head[u];
+                        if (head[u] < MK) {
+                            hv[u] = part_sim[base + (size_t)l * MK + head[u]];
+                            hrow[u] = part_row[base + (size_t)l * MK + head[u]];
+                        } else {
+                            hrow[u] = -1;
+                        }
+                    }
                 }
             }
         }
@@ -185,14 +208,15 @@ __global__ void merge_ranks_kernel(const double* __restrict__ d_all, const uint3
 }  // namespace lmi
 
 extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, const int32_t* slot_of_pair,
-                              const int32_t* bucket_order, const int64_t* bucket_off, const uint32_t* ids, int nq,
-                              int B, int C, int range_len, int rmax, int k_out, double* dists, uint32_t* nns,
-                              void* stream) {
-    if (!part_sim || !part_row || !slot_of_pair || !bucket_order || !bucket_off || !ids || !dists || !nns)
+                              const int32_t* bucket_order, const int64_t* bucket_off, const uint32_t* ids,
+                              const int32_t* bucket_lists, int nq, int B, int C, int lmax, int k_out, double* dists,
+                              uint32_t* nns, void* stream) {
+    if (!part_sim || !part_row || !slot_of_pair || !bucket_order || !bucket_off || !ids || !bucket_lists || !dists ||
+        !nns)
         return LMI_E_BADARG;
-    if (nq < 0 || B <= 0 || C <= 0 || range_len <= 0 || rmax <= 0 || k_out <= 0) return LMI_E_BADARG;
+    if (nq < 0 || B <= 0 || C <= 0 || lmax <= 0 || k_out <= 0) return LMI_E_BADARG;
     if (k_out > B * lmi::MK) return LMI_E_BADARG;
-    if (rmax > 32) return LMI_E_UNSUPPORTED;
+    if (lmax > 32 * lmi::MERGE_LPL) return LMI_E_UNSUPPORTED;
     if (nq == 0) return 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t per_warp = (size_t)2 * B * lmi::MK * sizeof(float);
@@ -207,7 +231,7 @@ extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, co
     }
     const int grid = (nq + warps - 1) / warps;
     lmi::merge_topk_kernel<<<grid, warps * 32, smem, st>>>(part_sim, part_row, slot_of_pair, bucket_order, bucket_off,
-                                                           ids, nq, B, C, range_len, rmax, k_out, dists, nns);
+                                                           ids, bucket_lists, nq, B, C, lmax, k_out, dists, nns);
     return static_cast<int>(cudaGetLastError());
 }
 

@@ -31,13 +31,15 @@ constexpr int SCAN_BOX_BYTES = SCAN_N * 128;  // one TMA box: 64 rows x 64 fp16
 constexpr int SCAN_BOXES = 4;                  // boxes (k-blocks) per pipeline stage: one barrier round-trip per 16 MMAs
 constexpr int SCAN_STAGE_BYTES = SCAN_BOXES * SCAN_BOX_BYTES;
 constexpr int SCAN_STAGES = 6;
-constexpr int SCAN_THREADS = 192;
+constexpr int SCAN_EPI_WARPS = 8;
+constexpr int TMA_WARP = SCAN_EPI_WARPS, MMA_WARP = SCAN_EPI_WARPS + 1;
+constexpr int SCAN_THREADS = (SCAN_EPI_WARPS + 2) * 32;
 constexpr int SCAN_MAX_D = 768;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t TMEM_ACC_COL = SCAN_MAX_D / 2;  // A: columns [0,384); accumulators: [384,448), [448,512)
 constexpr int TOPK = LMI_PER_BUCKET_K;
-constexpr int SCAN_EPI_COLS = 16;     // accumulator columns the epilogue pulls from TMEM per step
-constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
+constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ +
+                                   2 * SCAN_M * sizeof(float) /*gates*/;
 
 struct ScanBarriers {
     uint64_t full[SCAN_STAGES];
@@ -93,11 +95,12 @@ __device__ __forceinline__ void store_topk(const TopK& tk, float* __restrict__ p
 __global__ void __launch_bounds__(SCAN_THREADS, 1)
 scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __restrict__ Q,
                     const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
-                    const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int rmax,
+                    const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int lmax,
                     float* __restrict__ part_sim, int32_t* __restrict__ part_row) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     ScanBarriers* bars = reinterpret_cast<ScanBarriers*>(stages + (size_t)SCAN_STAGES * SCAN_STAGE_BYTES);
+    float* gates = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // [2 halves][128 rows]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -105,7 +108,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
     int n_items = *n_items_ptr;
     if ((int64_t)n_items > max_items) n_items = (int)max_items;
 
-    if (warp == 4 && lane == 0) {
+    if (warp == TMA_WARP && lane == 0) {
         ptx::tma_prefetch_desc(&tmap);
         for (int s = 0; s < SCAN_STAGES; ++s) {
             ptx::mbar_init(&bars->full[s], 1);
@@ -113,12 +116,12 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(&bars->acc_full[b], 1);
-            ptx::mbar_init(&bars->acc_empty[b], SCAN_M);
+            ptx::mbar_init(&bars->acc_empty[b], SCAN_EPI_WARPS);
         }
-        ptx::mbar_init(&bars->q_ready, SCAN_M);
+        ptx::mbar_init(&bars->q_ready, SCAN_EPI_WARPS * 32);
         ptx::fence_barrier_init();
     }
-    if (warp == 5) {
+    if (warp == MMA_WARP) {
         ptx::tmem_alloc(&bars->tmem_base, TMEM_COLS);
         ptx::tmem_relinquish();
     }
@@ -127,7 +130,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
     ptx::tc_fence_after();
     const uint32_t tmem = bars->tmem_base;
 
-    if (warp == 4) {
+    if (warp == TMA_WARP) {
         // ===================== TMA producer =====================
         // The whole warp walks the loop (warp-uniform control flow); one elected lane issues, so
         // ptxas emits the TMA / mbarrier instructions straight, without a per-thread waterfall loop.
@@ -158,7 +161,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 }
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == MMA_WARP) {
         // ===================== MMA issuer =====================
         constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;
@@ -205,21 +208,30 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         }
     } else {
         // ===================== epilogue warps (thread == query row) =====================
-        const int row = warp * 32 + lane;
-        const uint32_t lane_field = static_cast<uint32_t>(warp * 32) << 16;
+        // 8 warps: warp w reads TMEM lanes [32*(w&3), +32) (the hardware's lane quarter of warp
+        // w%4) and the 32-column half h = w>>2 of every 64-column score tile, so two warps per
+        // scheduler hide each other's TMEM-load and branch latencies.  Each (row, half) keeps its
+        // own top-10 list; the two halves gate on the larger of their 10th-best (exchanged through
+        // shared memory) and the merge kernel folds the lists with a (similarity, row) key.
+        const int q4 = warp & 3, h = warp >> 2;
+        const int row = q4 * 32 + lane;
+        const uint32_t lane_field = static_cast<uint32_t>(q4 * 32) << 16;
+        float* gate_mine = gates + h * SCAN_M + row;
+        const float* gate_other = gates + (h ^ 1) * SCAN_M + row;
         uint32_t tcount = 0;
         for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
             const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
-            const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, range_idx = w1.x;
+            const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
             const bool valid = row < mvalid;
 
-            // gather this item's query rows into TMEM (all MMAs of the previous item have
-            // completed: this warp consumed its last accumulator tile)
+            // gather this item's query rows into TMEM; half h takes the k-blocks c with c % 2 == h
+            // (all MMAs of the previous item have completed: every epilogue warp consumed its
+            // last accumulator tile before getting here)
             const int q = valid ? (pair_list[slot0 + row] / B) : 0;
             const uint4* qsrc = reinterpret_cast<const uint4*>(Q + (size_t)q * d);
-            for (int c = 0; c < KB; ++c) {
+            for (int c = h; c < KB; c += 2) {
                 uint32_t r[32];
                 if (valid) {
 #pragma unroll
@@ -237,50 +249,84 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), r);
             }
             ptx::tmem_st_wait();
+            *gate_mine = -INFINITY;
             ptx::tc_fence_before();
             ptx::mbar_arrive(&bars->q_ready);
 
             TopK tk;
             tk.reset();
+            float tau = -INFINITY;  // gate: a lower bound of this (row, range)'s final 10th best
             for (int t = 0; t < ntiles; ++t, ++tcount) {
                 const uint32_t buf = tcount & 1;
                 ptx::mbar_wait(&bars->acc_full[buf], (tcount >> 1) & 1);
                 ptx::tc_fence_after();
-                const uint32_t taddr = tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N;
-                const int base_row = row0 + t * SCAN_N;
-                const int live = nrows - t * SCAN_N;  // rows of this tile that belong to the range
-                // Rolled on purpose: the whole top-10 bookkeeping must stay resident in the
-                // instruction cache (a fully unrolled 64-column version is > 100 KB of SASS and
-                // ran fetch-bound).  16 columns at a time: one max-reduction rejects the chunk
-                // unless some lane of the warp holds a candidate.
-#pragma unroll 1
-                for (int c = 0; c < SCAN_N; c += SCAN_EPI_COLS) {
-                    uint32_t v[SCAN_EPI_COLS];
-                    ptx::tmem_ld16(taddr + c, v);
-                    ptx::tmem_ld_wait();
-                    float m = __uint_as_float(v[0]);
+                uint32_t v[32];
+                ptx::tmem_ld32(tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N + h * 32, v);
+                // the other half's 10th best, nudged down so that an exact tie with it still
+                // reaches the (similarity, row)-keyed merge
+                const float og = *gate_other;
+                tau = fmaxf(tau, og - fabsf(og) * 2.4e-7f);
+                ptx::tmem_ld_wait();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&bars->acc_empty[buf]);  // scores are in registers now
+
+                const int base_row = row0 + t * SCAN_N + h * 32;
+                const int lim = nrows - t * SCAN_N - h * 32;  // columns of this half inside the range
+                if (lim < 32) {
 #pragma unroll
-                    for (int j = 1; j < SCAN_EPI_COLS; ++j) m = fmaxf(m, __uint_as_float(v[j]));
-                    const int lim = live - c;  // columns of this chunk inside the range
-                    const bool cand = lim > 0 && m > tk.s[TOPK - 1];
-                    if (__any_sync(0xffffffffu, cand)) {
+                    for (int j = 0; j < 32; ++j)
+                        if (j >= lim) v[j] = 0xff800000u;  // -inf
+                }
+                float g[4];
 #pragma unroll
-                        for (int j = 0; j < SCAN_EPI_COLS; ++j) {
-                            const float f = __uint_as_float(v[j]);
-                            if (j < lim && f > tk.s[TOPK - 1]) tk.insert(f, base_row + c + j);
+                for (int gi = 0; gi < 4; ++gi) {
+                    float m = __uint_as_float(v[gi * 8]);
+#pragma unroll
+                    for (int j = 1; j < 8; ++j) m = fmaxf(m, __uint_as_float(v[gi * 8 + j]));
+                    g[gi] = m;
+                }
+                const float mall = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
+                if (__any_sync(0xffffffffu, mall > tau)) {
+#pragma unroll
+                    for (int gi = 0; gi < 4; ++gi) {
+                        if (__any_sync(0xffffffffu, g[gi] > tau)) {
+                            uint32_t mask = 0;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                mask |= (__uint_as_float(v[gi * 8 + j]) > tau) ? (1u << j) : 0u;
+                            // every lane pops its own lowest candidate column per trip, so lanes with
+                            // candidates in different columns share one pass through the insertion code
+                            while (__any_sync(0xffffffffu, mask != 0)) {
+                                if (mask != 0) {
+                                    const int j = __ffs(mask) - 1;
+                                    mask &= mask - 1;
+                                    const uint32_t a0 = (j & 1) ? v[gi * 8 + 1] : v[gi * 8 + 0];
+                                    const uint32_t a1 = (j & 1) ? v[gi * 8 + 3] : v[gi * 8 + 2];
+                                    const uint32_t a2 = (j & 1) ? v[gi * 8 + 5] : v[gi * 8 + 4];
+                                    const uint32_t a3 = (j & 1) ? v[gi * 8 + 7] : v[gi * 8 + 6];
+                                    const uint32_t b0 = (j & 2) ? a1 : a0;
+                                    const uint32_t b1 = (j & 2) ? a3 : a2;
+                                    const float f = __uint_as_float((j & 4) ? b1 : b0);
+                                    if (f > tau) {
+                                        tk.insert(f, base_row + gi * 8 + j);
+                                        tau = fmaxf(tau, tk.s[TOPK - 1]);
+                                    }
+                                }
+                            }
                         }
                     }
+                    *gate_mine = tk.s[TOPK - 1];
                 }
-                ptx::tc_fence_before();
-                ptx::mbar_arrive(&bars->acc_empty[buf]);
             }
-            if (valid) store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * rmax + range_idx) * TOPK);
+            if (valid)
+                store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * lmax + list0 + h) * TOPK);
         }
     }
 
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 5) {
+    if (warp == MMA_WARP) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc(tmem, TMEM_COLS);
     }
@@ -291,7 +337,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
 __global__ void __launch_bounds__(SCAN_M)
 scan_topk_simt_kernel(const __half* __restrict__ X, const __half* __restrict__ Q,
                       const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
-                      const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int rmax,
+                      const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int lmax,
                       float* __restrict__ part_sim, int32_t* __restrict__ part_row) {
     extern __shared__ __half xs[];  // one row of X
     int n_items = *n_items_ptr;
@@ -299,7 +345,7 @@ scan_topk_simt_kernel(const __half* __restrict__ X, const __half* __restrict__ Q
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
         const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
-        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, range_idx = w1.x;
+        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
         const int row = threadIdx.x;
         const bool valid = row < mvalid;
         const int q = valid ? (pair_list[slot0 + row] / B) : 0;
@@ -317,7 +363,11 @@ scan_topk_simt_kernel(const __half* __restrict__ X, const __half* __restrict__ Q
                 tk.offer(acc, row0 + r);
             }
         }
-        if (valid) store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * rmax + range_idx) * TOPK);
+        if (valid) {
+            store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * lmax + list0) * TOPK);
+            tk.reset();  // the item's second list (the tcgen05 kernel's other column half) stays empty
+            store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * lmax + list0 + 1) * TOPK);
+        }
     }
 }
 
@@ -341,10 +391,10 @@ static EncodeTiledFn get_encode_fn() {
 
 extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int nq, int B,
                              const int32_t* pair_list, const int32_t* items, const int32_t* n_items,
-                             int64_t max_items, int rmax, float* part_sim, int32_t* part_row, int impl,
+                             int64_t max_items, int lmax, float* part_sim, int32_t* part_row, int impl,
                              void* stream) {
     if (!X || !Q || !pair_list || !items || !n_items || !part_sim || !part_row) return LMI_E_BADARG;
-    if (n <= 0 || d <= 0 || nq <= 0 || B <= 0 || rmax <= 0 || max_items <= 0) return LMI_E_BADARG;
+    if (n <= 0 || d <= 0 || nq <= 0 || B <= 0 || lmax <= 0 || max_items <= 0) return LMI_E_BADARG;
     if (n > 0x7fffffffLL) return LMI_E_UNSUPPORTED;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int dev = 0, sms = 0;
@@ -356,7 +406,7 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
         const int grid = (int)(max_items < (int64_t)sms * 8 ? max_items : (int64_t)sms * 8);
         lmi::scan_topk_simt_kernel<<<grid, lmi::SCAN_M, (size_t)d * sizeof(__half), st>>>(
             static_cast<const __half*>(X), static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d,
-            rmax, part_sim, part_row);
+            lmax, part_sim, part_row);
         return static_cast<int>(cudaGetLastError());
     }
     if (impl != 0) return LMI_E_BADARG;
@@ -384,6 +434,6 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
     }
     const int grid = (int)(max_items < (int64_t)sms ? max_items : (int64_t)sms);
     lmi::scan_topk_tc_kernel<<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
-        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, rmax, part_sim, part_row);
+        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row);
     return static_cast<int>(cudaGetLastError());
 }

@@ -69,6 +69,7 @@ def test_invert_matches_numpy():
         max_items = int(L.lmi_max_items(nq, B, C, rmax))
         d_counts = torch.empty(C, dtype=torch.int32, device=dev)
         d_off = torch.empty(C + 1, dtype=torch.int32, device=dev)
+        d_bl = torch.full((C,), -7, dtype=torch.int32, device=dev)
         d_pl = torch.full((P,), -7, dtype=torch.int32, device=dev)
         d_sop = torch.full((P,), -7, dtype=torch.int32, device=dev)
         d_items = torch.zeros(max_items * 8, dtype=torch.int32, device=dev)
@@ -76,7 +77,8 @@ def test_invert_matches_numpy():
         work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
         d_order, d_boff = t(order), t(off)
         _native.check(L.lmi_invert(d_order.data_ptr(), nq, B, C, d_boff.data_ptr(), rng_len, d_counts.data_ptr(),
-                                   d_off.data_ptr(), d_pl.data_ptr(), d_sop.data_ptr(), d_items.data_ptr(),
+                                   d_off.data_ptr(), d_bl.data_ptr(), d_pl.data_ptr(), d_sop.data_ptr(),
+                                   d_items.data_ptr(),
                                    d_n.data_ptr(), max_items, work.data_ptr(), 0))
         torch.cuda.synchronize()
         flat = order.reshape(-1)
@@ -102,7 +104,9 @@ def test_invert_matches_numpy():
             for r in range(-(-s // rng_len)):
                 for tq in range(-(-m // 128)):
                     exp_items.append((off[b] + r * rng_len, min(rng_len, s - r * rng_len), exp_off[b] + tq * 128,
-                                      min(128, m - tq * 128), r, b, 0, 0))
+                                      min(128, m - tq * 128), 2 * r, b, 0, 0))
+        exp_bl = np.where((exp_counts > 0) & (sizes > 0), 2 * -(-sizes // rng_len), 0)
+        assert np.array_equal(d_bl.cpu().numpy(), exp_bl)
         assert n_items == len(exp_items) <= max_items
         assert np.array_equal(items, np.array(exp_items, dtype=np.int32).reshape(-1, 8))
 
