@@ -96,7 +96,9 @@ int64_t lmi_invert_workspace_ints(int nq, int B, int C);
  * cuts the scan into work items.
  *   bucket_order int32[nq,B]   in   (entries outside [0,C) are ignored)
  *   bucket_off   int64[C+1]    in   row range of bucket b in the bucket-major matrix
- *   range_len                  in   rows per work item (multiple of 64)
+ *   range_len                  in   upper bound on the rows of a work item (multiple of 64); a
+ *                                   bucket of s rows is cut into ceil(s / range_len) ranges of
+ *                                   equal length, rounded up to a multiple of 64
  *   counts       int32[C]      out  m_b = pairs probing bucket b
  *   offsets      int32[C+1]    out  exclusive scan of counts
  *   bucket_lists int32[C]      out  partial lists the scan writes per (query, bucket b) pair
@@ -104,7 +106,7 @@ int64_t lmi_invert_workspace_ints(int nq, int B, int C);
  *   pair_list    int32[nq*B]   out  flat pair index per sorted slot
  *   slot_of_pair int32[nq*B]   out  inverse permutation (-1 for ignored pairs)
  *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, first list, bucket, 0, 0}
- *   n_items      int32[1]      out
+ *   n_items      int32[2]      out  [0] number of items; [1] scratch (the scan's scheduler counter)
  *   workspace    int32[lmi_invert_workspace_ints(nq,B,C)]  scratch
  */
 int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t *bucket_off,

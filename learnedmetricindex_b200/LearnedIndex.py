@@ -16,6 +16,7 @@ the union of each query's per-bucket top-10 lists; that is what the fused pass c
 """
 from __future__ import annotations
 
+import os
 import time
 from collections import defaultdict
 from typing import Dict, List, Optional, Tuple
@@ -32,6 +33,7 @@ PER_BUCKET_K = 10  # `k` is not forwarded to _search_single_bucket (LearnedIndex
 MAX_RANGES = 32  # row ranges a bucket is cut into at most
 LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
+DEFAULT_RANGE_ROWS = 8192  # upper bound on the rows of a scan work item (see plan_scan)
 
 
 def _stream_ptr() -> int:
@@ -53,6 +55,9 @@ def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_b
     total_rows = tiles * mean_bucket
     want = max(1, n_sms * items_per_sm)
     length = -(-total_rows // want)
+    # short ranges keep the dynamic schedule balanced and the query tiles of a range within an L2
+    # window of each other; long enough that the per-item query gather and top-10 warm-up amortise
+    length = min(length, int(os.environ.get("LMI_RANGE_ROWS", DEFAULT_RANGE_ROWS)))
     length = max(length, 1024, -(-max_bucket // MAX_RANGES))
     length = min(length, max(max_bucket, SCAN_ROWS_PER_TILE))
     length = -(-length // SCAN_ROWS_PER_TILE) * SCAN_ROWS_PER_TILE
@@ -184,7 +189,7 @@ class LearnedIndex:
         pair_list = torch.empty(P, dtype=torch.int32, device=dev)
         slot_of_pair = torch.empty(P, dtype=torch.int32, device=dev)
         items = torch.empty(max_items * 8, dtype=torch.int32, device=dev)
-        n_items = torch.zeros(1, dtype=torch.int32, device=dev)
+        n_items = torch.zeros(2, dtype=torch.int32, device=dev)
         work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
         _native.check(L.lmi_invert(order.data_ptr(), nq, B, C, layout.bucket_off.data_ptr(), range_len,
                                    counts.data_ptr(), offsets.data_ptr(), bucket_lists.data_ptr(), pair_list.data_ptr(),

@@ -105,12 +105,16 @@ invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __re
         if (c < C) offsets[c] = off;
 
         int nr = 0, nt = 0;
-        int64_t lo = 0, hi = 0;
+        int64_t lo = 0, hi = 0, len = 0;
         if (c < C && m > 0) {
             lo = bucket_off[c];
             hi = bucket_off[c + 1];
             if (hi > lo) {
+                // ranges of equal length (a multiple of 64 rows, <= range_len): the items of a
+                // bucket then take equally long, which keeps the scan's in-order dynamic schedule
+                // balanced and the query tiles of one range in step
                 nr = (int)((hi - lo + range_len - 1) / range_len);
+                len = ((hi - lo + nr - 1) / nr + 63) / 64 * 64;
                 nt = (m + SCAN_M_TILE - 1) / SCAN_M_TILE;
             }
         }
@@ -118,8 +122,8 @@ invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __re
         int tot_items;
         const int ibase = block_exclusive_scan(nr * nt, warp_tot, tot_items) + carry_items;
         for (int r = 0; r < nr; ++r) {
-            const int64_t row0 = lo + (int64_t)r * range_len;
-            const int nrows = (int)min((int64_t)range_len, hi - row0);
+            const int64_t row0 = lo + (int64_t)r * len;
+            const int nrows = (int)min(len, hi - row0);
             for (int t = 0; t < nt; ++t) {
                 const int64_t idx = (int64_t)ibase + (int64_t)r * nt + t;
                 if (idx >= max_items) continue;

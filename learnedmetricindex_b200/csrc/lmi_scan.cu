@@ -38,6 +38,7 @@ constexpr int SCAN_MAX_D = 768;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t TMEM_ACC_COL = SCAN_MAX_D / 2;  // A: columns [0,384); accumulators: [384,448), [448,512)
 constexpr int TOPK = LMI_PER_BUCKET_K;
+constexpr int SCAN_SCHED_SLOTS = 4;   // item indices the producer may run ahead of the consumers
 constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ +
                                    2 * SCAN_M * sizeof(float) /*gates*/;
 
@@ -47,6 +48,9 @@ struct ScanBarriers {
     uint64_t acc_full[2];
     uint64_t acc_empty[2];
     uint64_t q_ready;
+    uint64_t sched_full[SCAN_SCHED_SLOTS];
+    uint64_t sched_empty[SCAN_SCHED_SLOTS];
+    int32_t sched_item[SCAN_SCHED_SLOTS];
     uint32_t tmem_base;
 };
 static_assert(sizeof(ScanBarriers) <= 512, "barrier block too large");
@@ -107,6 +111,23 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
     const int KB = d / SCAN_KBLK;
     int n_items = *n_items_ptr;
     if ((int64_t)n_items > max_items) n_items = (int)max_items;
+    // Dynamic in-order scheduling: the producer warp draws item indices from a global counter and
+    // hands them to the MMA and epilogue warps through a small shared-memory ring.  Items of one
+    // (bucket, row range) -- one per tile of 128 probing queries -- are adjacent in the list, so
+    // they are drawn back to back by CTAs that stream the same rows at the same time: the
+    // range is read from HBM once and from L2 by the other query tiles.
+    int* sched_counter = const_cast<int*>(n_items_ptr) + 1;
+    auto next_item = [&](uint32_t& slot, uint32_t& phase) -> int {
+        ptx::mbar_wait(&bars->sched_full[slot], phase);
+        const int it = *reinterpret_cast<volatile int32_t*>(&bars->sched_item[slot]);
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bars->sched_empty[slot]);
+        if (++slot == SCAN_SCHED_SLOTS) {
+            slot = 0;
+            phase ^= 1;
+        }
+        return it;
+    };
 
     if (warp == TMA_WARP && lane == 0) {
         ptx::tma_prefetch_desc(&tmap);
@@ -119,6 +140,10 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             ptx::mbar_init(&bars->acc_empty[b], SCAN_EPI_WARPS);
         }
         ptx::mbar_init(&bars->q_ready, SCAN_EPI_WARPS * 32);
+        for (int b = 0; b < SCAN_SCHED_SLOTS; ++b) {
+            ptx::mbar_init(&bars->sched_full[b], 1);
+            ptx::mbar_init(&bars->sched_empty[b], SCAN_EPI_WARPS + 1);
+        }
         ptx::fence_barrier_init();
     }
     if (warp == MMA_WARP) {
@@ -136,8 +161,22 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         // ptxas emits the TMA / mbarrier instructions straight, without a per-thread waterfall loop.
         const uint64_t policy = ptx::policy_evict_normal();
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;  // stages per 64-row tile
-        uint32_t stage = 0, phase = 0;
-        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        uint32_t stage = 0, phase = 0, sslot = 0, sphase = 0;
+        while (true) {
+            ptx::mbar_wait(&bars->sched_empty[sslot], sphase ^ 1);
+            int it = 0;
+            if (lane == 0) it = atomicAdd(sched_counter, 1);
+            it = __shfl_sync(0xffffffffu, it, 0);
+            if (it >= n_items) it = -1;
+            if (lane == 0) {
+                *reinterpret_cast<volatile int32_t*>(&bars->sched_item[sslot]) = it;
+                ptx::mbar_arrive(&bars->sched_full[sslot]);
+            }
+            if (++sslot == SCAN_SCHED_SLOTS) {
+                sslot = 0;
+                sphase ^= 1;
+            }
+            if (it < 0) break;
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
             const int row0 = w0.x, nrows = w0.y;
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
@@ -166,8 +205,10 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;
         const uint64_t desc0 = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(stages));
-        uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0;
-        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0, sslot = 0, sphase = 0;
+        while (true) {
+            const int it = next_item(sslot, sphase);
+            if (it < 0) break;
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
             const int nrows = w0.y;
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
@@ -218,8 +259,10 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         const uint32_t lane_field = static_cast<uint32_t>(q4 * 32) << 16;
         float* gate_mine = gates + h * SCAN_M + row;
         const float* gate_other = gates + (h ^ 1) * SCAN_M + row;
-        uint32_t tcount = 0;
-        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        uint32_t tcount = 0, sslot = 0, sphase = 0;
+        while (true) {
+            const int it = next_item(sslot, sphase);
+            if (it < 0) break;
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
             const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
             const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
@@ -433,6 +476,8 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
         attr_set = true;
     }
     const int grid = (int)(max_items < (int64_t)sms ? max_items : (int64_t)sms);
+    cudaError_t me = cudaMemsetAsync(const_cast<int32_t*>(n_items) + 1, 0, sizeof(int32_t), st);  // scheduler counter
+    if (me != cudaSuccess) return (int)me;
     lmi::scan_topk_tc_kernel<<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
         tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row);
     return static_cast<int>(cudaGetLastError());

@@ -73,7 +73,7 @@ def test_invert_matches_numpy():
         d_pl = torch.full((P,), -7, dtype=torch.int32, device=dev)
         d_sop = torch.full((P,), -7, dtype=torch.int32, device=dev)
         d_items = torch.zeros(max_items * 8, dtype=torch.int32, device=dev)
-        d_n = torch.zeros(1, dtype=torch.int32, device=dev)
+        d_n = torch.zeros(2, dtype=torch.int32, device=dev)
         work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
         d_order, d_boff = t(order), t(off)
         _native.check(L.lmi_invert(d_order.data_ptr(), nq, B, C, d_boff.data_ptr(), rng_len, d_counts.data_ptr(),
@@ -94,16 +94,18 @@ def test_invert_matches_numpy():
         assert np.array_equal(sop[exp_pl], np.arange(valid.sum()))
         assert (sop[~valid] == -1).all()
         # work items: every (bucket with m>0 and rows>0) x range x query tile exactly once
-        n_items = int(d_n.item())
+        n_items = int(d_n[0].item())
         items = d_items.cpu().numpy().reshape(-1, 8)[:n_items]
         exp_items = []
         for b in range(C):
             m, s = exp_counts[b], sizes[b]
             if m == 0 or s == 0:
                 continue
-            for r in range(-(-s // rng_len)):
+            nr = -(-s // rng_len)
+            ln = -(-(-(-s // nr)) // 64) * 64  # equal ranges, rounded up to 64 rows
+            for r in range(nr):
                 for tq in range(-(-m // 128)):
-                    exp_items.append((off[b] + r * rng_len, min(rng_len, s - r * rng_len), exp_off[b] + tq * 128,
+                    exp_items.append((off[b] + r * ln, min(ln, s - r * ln), exp_off[b] + tq * 128,
                                       min(128, m - tq * 128), 2 * r, b, 0, 0))
         exp_bl = np.where((exp_counts > 0) & (sizes > 0), 2 * -(-sizes // rng_len), 0)
         assert np.array_equal(d_bl.cpu().numpy(), exp_bl)
