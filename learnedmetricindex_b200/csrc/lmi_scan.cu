@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/lmi_b200.h"
 #include "lmi_ptx.cuh"
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 1)
 scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __restrict__ Q,
                     const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
                     const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int lmax,
-                    float* __restrict__ part_sim, int32_t* __restrict__ part_row) {
+                    float* __restrict__ part_sim, int32_t* __restrict__ part_row, int dbg) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     ScanBarriers* bars = reinterpret_cast<ScanBarriers*>(stages + (size_t)SCAN_STAGES * SCAN_STAGE_BYTES);
@@ -183,11 +184,16 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             for (int t = 0; t < ntiles; ++t) {
                 for (int s = 0; s < SPT; ++s) {
                     const int kb0 = s * SCAN_BOXES;
-                    const int nb = min(SCAN_BOXES, KB - kb0);
+                    int nb = min(SCAN_BOXES, KB - kb0);
                     ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
                     if (ptx::elect_one()) {
                         uint8_t* dst = stages + (size_t)stage * SCAN_STAGE_BYTES;
-                        ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
+                        if (dbg & 1) {  // ablation: no loads, the MMAs run on whatever the stage holds
+                            ptx::mbar_arrive(&bars->full[stage]);
+                            nb = 0;
+                        } else {
+                            ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
+                        }
                         for (int b = 0; b < nb; ++b)
                             ptx::tma_load_2d(dst + b * SCAN_BOX_BYTES, &tmap, (kb0 + b) * SCAN_KBLK, row0 + t * SCAN_N,
                                              &bars->full[stage], policy);
@@ -205,6 +211,8 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;
         const uint64_t desc0 = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(stages));
+        const uint32_t desc0_lo = (uint32_t)desc0;
+        const uint64_t desc0_hi = desc0 >> 32;
         uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0, sslot = 0, sphase = 0;
         while (true) {
             const int it = next_item(sslot, sphase);
@@ -226,14 +234,32 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     ptx::mbar_wait(&bars->full[stage], phase);
                     ptx::tc_fence_after();
                     if (ptx::elect_one()) {
-                        // descriptor start-address field counts 16-byte units: stage and box offsets add linearly
-                        const uint64_t sdesc = desc0 + (uint64_t)((stage * SCAN_STAGE_BYTES) >> 4);
-                        for (int b = 0; b < nb; ++b) {
+                        // The descriptor's start-address field counts 16-byte units in its low word,
+                        // so stage / box / k offsets are plain adds on that word.  A full stage is
+                        // issued as 16 straight-line MMAs whose operands differ from the stage base
+                        // by compile-time constants (no dependent address arithmetic between them).
+                        const uint32_t dlo = desc0_lo + ((stage * SCAN_STAGE_BYTES) >> 4);
+                        const uint32_t a0 = tmem + kb0 * (SCAN_KBLK / 2);
+                        if (nb == SCAN_BOXES) {
 #pragma unroll
-                            for (int k = 0; k < SCAN_KBLK / 16; ++k) {
-                                const uint64_t b_desc = sdesc + (uint64_t)((b * SCAN_BOX_BYTES + k * 32) >> 4);
-                                const uint32_t a_tmem = tmem + (kb0 + b) * (SCAN_KBLK / 2) + k * 8;
-                                ptx::mma_f16_ts(d_tmem, a_tmem, b_desc, idesc, (s | b | k) != 0 ? 1u : 0u);
+                            for (int b = 0; b < SCAN_BOXES; ++b) {
+#pragma unroll
+                                for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                                    const uint64_t b_desc =
+                                        (desc0_hi << 32) | (uint64_t)(dlo + ((b * SCAN_BOX_BYTES + k * 32) >> 4));
+                                    ptx::mma_f16_ts(d_tmem, a0 + b * (SCAN_KBLK / 2) + k * 8, b_desc, idesc,
+                                                    (b | k) != 0 ? 1u : (s != 0 ? 1u : 0u));
+                                }
+                            }
+                        } else {
+                            for (int b = 0; b < nb; ++b) {
+#pragma unroll
+                                for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                                    const uint64_t b_desc =
+                                        (desc0_hi << 32) | (uint64_t)(dlo + ((b * SCAN_BOX_BYTES + k * 32) >> 4));
+                                    ptx::mma_f16_ts(d_tmem, a0 + b * (SCAN_KBLK / 2) + k * 8, b_desc, idesc,
+                                                    (s | b | k) != 0 ? 1u : 0u);
+                                }
                             }
                         }
                         ptx::mma_commit(&bars->empty[stage]);
@@ -330,7 +356,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     g[gi] = m;
                 }
                 const float mall = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
-                if (__any_sync(0xffffffffu, mall > tau)) {
+                if ((dbg & 2) == 0 && __any_sync(0xffffffffu, mall > tau)) {
 #pragma unroll
                     for (int gi = 0; gi < 4; ++gi) {
                         if (__any_sync(0xffffffffu, g[gi] > tau)) {
@@ -476,9 +502,11 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
         attr_set = true;
     }
     const int grid = (int)(max_items < (int64_t)sms ? max_items : (int64_t)sms);
+    const char* dbg_env = getenv("LMI_SCAN_ABLATE");  // profiling ablations only; results are wrong when set
+    const int dbg = dbg_env ? atoi(dbg_env) : 0;
     cudaError_t me = cudaMemsetAsync(const_cast<int32_t*>(n_items) + 1, 0, sizeof(int32_t), st);  // scheduler counter
     if (me != cudaSuccess) return (int)me;
     lmi::scan_topk_tc_kernel<<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
-        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row);
+        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row, dbg);
     return static_cast<int>(cudaGetLastError());
 }
