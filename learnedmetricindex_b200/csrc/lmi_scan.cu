@@ -33,8 +33,9 @@ constexpr int SCAN_BOXES = 4;                  // boxes (k-blocks) per pipeline 
 constexpr int SCAN_STAGE_BYTES = SCAN_BOXES * SCAN_BOX_BYTES;
 constexpr int SCAN_STAGES = 6;
 constexpr int SCAN_EPI_WARPS = 8;
-constexpr int TMA_WARP = SCAN_EPI_WARPS, MMA_WARP = SCAN_EPI_WARPS + 1;
-constexpr int SCAN_THREADS = (SCAN_EPI_WARPS + 2) * 32;
+constexpr int TMA_WARP = SCAN_EPI_WARPS, MMA_WARP = SCAN_EPI_WARPS + 1;  // MMA issuers: warps MMA_WARP, MMA_WARP + 1
+constexpr int SCAN_MMA_WARPS = 2;
+constexpr int SCAN_THREADS = (SCAN_EPI_WARPS + 1 + SCAN_MMA_WARPS) * 32;
 constexpr int SCAN_MAX_D = 768;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t TMEM_ACC_COL = SCAN_MAX_D / 2;  // A: columns [0,384); accumulators: [384,448), [448,512)
@@ -42,6 +43,9 @@ constexpr int TOPK = LMI_PER_BUCKET_K;
 constexpr int SCAN_SCHED_SLOTS = 4;   // item indices the producer may run ahead of the consumers
 constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ +
                                    2 * SCAN_M * sizeof(float) /*gates*/;
+
+// profiling aid (LMI_SCAN_ABLATE & 8): per CTA, cycles the MMA warp spent waiting on each barrier
+__device__ long long g_scan_prof[148 * 8];
 
 struct ScanBarriers {
     uint64_t full[SCAN_STAGES];
@@ -143,7 +147,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         ptx::mbar_init(&bars->q_ready, SCAN_EPI_WARPS * 32);
         for (int b = 0; b < SCAN_SCHED_SLOTS; ++b) {
             ptx::mbar_init(&bars->sched_full[b], 1);
-            ptx::mbar_init(&bars->sched_empty[b], SCAN_EPI_WARPS + 1);
+            ptx::mbar_init(&bars->sched_empty[b], SCAN_EPI_WARPS + SCAN_MMA_WARPS);
         }
         ptx::fence_barrier_init();
     }
@@ -206,33 +210,63 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 }
             }
         }
-    } else if (warp == MMA_WARP) {
-        // ===================== MMA issuer =====================
+    } else if (warp >= MMA_WARP) {
+        // ===================== MMA issuers =====================
+        // tcgen05.mma issue is synchronous with the tensor pipe (measured: the issuing thread
+        // advances one MMA per ~36 cycles and the pipe drains within one or two MMAs once it
+        // stops), so every barrier round trip of a single issuer is tensor-pipe idle time.  Two
+        // issuer warps therefore alternate by score tile: warp w owns the tiles with
+        // (tile counter & 1) == w, i.e. accumulator buffer w and every other group of SPT
+        // pipeline stages, and does its barrier waits while the other warp is issuing.
+        const uint32_t mw = warp - MMA_WARP;
         constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;
         const uint64_t desc0 = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(stages));
         const uint32_t desc0_lo = (uint32_t)desc0;
         const uint64_t desc0_hi = desc0 >> 32;
         uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0, sslot = 0, sphase = 0;
+        auto skip_tile_stages = [&]() {
+            for (int s = 0; s < SPT; ++s)
+                if (++stage == SCAN_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+        };
+        if (mw == 1) skip_tile_stages();
+        const bool prof = (dbg & 8) != 0 && mw == 0;
+        long long p_sched = 0, p_q = 0, p_acc = 0, p_full = 0, p_issue = 0, p_n = 0, p_t0 = clock64(), p_c;
+#define PROF_BEGIN() if (prof) p_c = clock64()
+#define PROF_END(acc) if (prof) acc += clock64() - p_c
         while (true) {
+            PROF_BEGIN();
             const int it = next_item(sslot, sphase);
+            PROF_END(p_sched);
             if (it < 0) break;
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
             const int nrows = w0.y;
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+            PROF_BEGIN();
             ptx::mbar_wait(&bars->q_ready, item_parity);
+            PROF_END(p_q);
             item_parity ^= 1;
             ptx::tc_fence_after();
             for (int t = 0; t < ntiles; ++t, ++tcount) {
                 const uint32_t buf = tcount & 1;
+                if (buf != mw) continue;
+                PROF_BEGIN();
                 ptx::mbar_wait(&bars->acc_empty[buf], ((tcount >> 1) & 1) ^ 1);
+                PROF_END(p_acc);
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem + TMEM_ACC_COL + buf * SCAN_N;
                 for (int s = 0; s < SPT; ++s) {
                     const int kb0 = s * SCAN_BOXES;
                     const int nb = min(SCAN_BOXES, KB - kb0);
+                    PROF_BEGIN();
                     ptx::mbar_wait(&bars->full[stage], phase);
+                    PROF_END(p_full);
                     ptx::tc_fence_after();
+                    PROF_BEGIN();
+                    ++p_n;
                     if (ptx::elect_one()) {
                         // The descriptor's start-address field counts 16-byte units in its low word,
                         // so stage / box / k offsets are plain adds on that word.  A full stage is
@@ -266,13 +300,21 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                         if (s == SPT - 1) ptx::mma_commit(&bars->acc_full[buf]);
                     }
                     __syncwarp();
+                    PROF_END(p_issue);
                     if (++stage == SCAN_STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
+                skip_tile_stages();  // the other issuer's tile
             }
         }
+        if (prof && lane == 0 && blockIdx.x < 148) {
+            long long* o = g_scan_prof + blockIdx.x * 8;
+            o[0] = clock64() - p_t0; o[1] = p_sched; o[2] = p_q; o[3] = p_acc; o[4] = p_full; o[5] = p_issue; o[6] = p_n;
+        }
+#undef PROF_BEGIN
+#undef PROF_END
     } else {
         // ===================== epilogue warps (thread == query row) =====================
         // 8 warps: warp w reads TMEM lanes [32*(w&3), +32) (the hardware's lane quarter of warp
@@ -457,6 +499,10 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 }  // namespace lmi
+
+extern "C" int lmi_debug_scan_profile(long long* host_out /* [148*8] */) {
+    return (int)cudaMemcpyFromSymbol(host_out, lmi::g_scan_prof, sizeof(long long) * 148 * 8);
+}
 
 extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int nq, int B,
                              const int32_t* pair_list, const int32_t* items, const int32_t* n_items,

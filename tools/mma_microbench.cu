@@ -7,7 +7,7 @@
 using namespace lmi;
 
 template <int N, bool A_TMEM, int NACC>
-__global__ void __launch_bounds__(128, 1) k_mma(int reps, int per_commit, long long* out, const uint8_t* src, int copy,
+__global__ void __launch_bounds__(320, 1) k_mma(int reps, int per_commit, long long* out, const uint8_t* src, int copy,
                                                volatile int* stop_flag_unused) {
     extern __shared__ uint8_t raw[];
     uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~uintptr_t(1023));
@@ -17,12 +17,26 @@ __global__ void __launch_bounds__(128, 1) k_mma(int reps, int per_commit, long l
     __shared__ long long copied;
     __shared__ uint32_t tbase;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < 96 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0;
+    for (int i = threadIdx.x; i < 96 * 1024 / 4; i += 320) reinterpret_cast<uint32_t*>(sm)[i] = 0;
     if (threadIdx.x == 0) { ptx::mbar_init(&bar, 1); for (int i = 0; i < 4; ++i) ptx::mbar_init(&cbar[i], 1); done = 0; copied = 0; ptx::fence_barrier_init(); }
     if (warp == 0) { ptx::tmem_alloc(&tbase, 512); ptx::tmem_relinquish(); }
     ptx::fence_proxy_async();
     ptx::tc_fence_before(); __syncthreads(); ptx::tc_fence_after();
     const uint32_t tmem = tbase;
+    __shared__ uint64_t never;
+    if (threadIdx.x == 0) ptx::mbar_init(&never, 1);
+    __syncthreads();
+    const int side = copy >> 4;  // 1: other 8 warps spin on an mbarrier; 2: they stream tcgen05.ld
+    if (warp >= 2 && warp < 10 && side) {
+        const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;
+        uint32_t acc = 0;
+        while (!done) {
+            if (side == 1) { acc += ptx::mbar_try_wait(&never, 0); }
+            else { uint32_t v[32]; ptx::tmem_ld32(tmem + lane_field + 256 + (warp >> 2) * 32, v); ptx::tmem_ld_wait(); acc += v[lane]; }
+        }
+        if (acc == 0x12345678u) out[0] = 1;
+    }
+    copy &= 15;
     if (warp == 1) {
         const uint32_t idesc = ptx::umma_idesc_f16(128, N);
         const uint64_t bdesc = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(sm));            // B: N rows x 64 fp16
@@ -47,7 +61,7 @@ __global__ void __launch_bounds__(128, 1) k_mma(int reps, int per_commit, long l
         }
         long long t1 = clock64();
         if (lane == 0) { out[blockIdx.x] = t1 - t0; done = 1; }
-    } else if (warp == 2 && copy) {
+    } else if (warp == 0 && copy) {
         // streams 8 KB bulk copies (L2-resident source) into a 4 x 8 KB ring at 32 KB.. of shared memory
         if (lane == 0) {
             uint32_t ph[4] = {0, 0, 0, 0};
@@ -78,10 +92,10 @@ void run(const char* name, int grid, int copy = 0) {
     auto kern = k_mma<N, A_TMEM, NACC>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     const int reps = 200, per = 64;
-    kern<<<grid, 128, 100 * 1024>>>(10, per, d, src, copy, nullptr);
+    kern<<<grid, 320, 100 * 1024>>>(10, per, d, src, copy, nullptr);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0);
-    kern<<<grid, 128, 100 * 1024>>>(reps, per, d, src, copy, nullptr);
+    kern<<<grid, 320, 100 * 1024>>>(reps, per, d, src, copy, nullptr);
     cudaEventRecord(e1);
     cudaError_t e = cudaDeviceSynchronize();
     float ms; cudaEventElapsedTime(&ms, e0, e1);
@@ -94,6 +108,10 @@ void run(const char* name, int grid, int copy = 0) {
 }
 
 int main() {
+    run<64, true, 2>("N=64 tmem, 8 warps spin", 148, 16);
+    run<64, true, 2>("N=64 tmem, 8 warps LDTM", 148, 32);
+    run<64, true, 2>("N=64 tmem, spin + copy", 148, 17);
+    run<64, true, 2>("N=64 tmem, LDTM + copy", 148, 33);
     run<64, true, 2>("N=64 A=tmem +copy", 1, 1);
     run<64, true, 2>("N=64 A=tmem +copy", 148, 1);
     run<128, true, 2>("N=128 A=tmem +copy", 148, 1);

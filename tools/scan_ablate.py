@@ -36,5 +36,21 @@ for R in [int(x) for x in a.ranges.split(",")]:
             li.search_device(Q, Q, [120], a.probe, 10, events=e)
         torch.cuda.synchronize()
         scan = np.mean([e[2].elapsed_time(e[3]) for e in evs])
+        if ab & 8:
+            import ctypes
+            from learnedmetricindex_b200 import _native
+            buf = (ctypes.c_longlong * (148 * 8))()
+            _native.lib().lmi_debug_scan_profile.argtypes = [ctypes.c_void_p]
+            _native.lib().lmi_debug_scan_profile(buf)
+            pr = np.array(buf[:]).reshape(148, 8)
+            names = ["total", "sched", "q_ready", "acc_empty", "full", "issue", "stages"]
+            print("   MMA-warp cycles (mean over CTAs):", {n: int(pr[:, i].mean()) for i, n in enumerate(names)},
+                  "total min/max", pr[:, 0].min(), pr[:, 0].max(), "stages min/max", pr[:, 6].min(), pr[:, 6].max())
+        import time
+        smp = bench.ClockSampler(0, period_s=0.005); smp.start(); t_a = time.time()
+        for _ in range(150):
+            li.search_device(Q, Q, [120], a.probe, 10)
+        torch.cuda.synchronize(); t_b = time.time(); smp.stop()
+        print("   clocks over %.2f s of back-to-back steps:" % (t_b - t_a), smp.summary([(t_a + 0.3, t_b)]))
         print(f"range_rows={R} ablate={ab}: scan {scan:.3f} ms  n_items={int(li.last_plan['n_items'][0])}", flush=True)
 os.environ["LMI_SCAN_ABLATE"] = "0"
