@@ -33,7 +33,7 @@ PER_BUCKET_K = 10  # `k` is not forwarded to _search_single_bucket (LearnedIndex
 MAX_RANGES = 32  # row ranges a bucket is cut into at most
 LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
-DEFAULT_RANGE_ROWS = 8192  # upper bound on the rows of a scan work item (see plan_scan)
+DEFAULT_RANGE_ROWS = 16384  # upper bound on the rows of a scan work item (see plan_scan)
 
 
 def _stream_ptr() -> int:

@@ -2,17 +2,24 @@
 // faiss.knn(..., METRIC_INNER_PRODUCT), search/li/LearnedIndex.py:350-365).
 //
 // Work item = (bucket, row range of <= range_len rows, tile of <= 128 probing queries).
-// Persistent CTAs (one per SM) walk the item list round-robin.  Per item:
+// Persistent CTAs (one per SM) draw items IN ORDER from a global counter; the items of one
+// (bucket, range) -- one per query tile -- are adjacent in the list, so they run at the same
+// time on different SMs and the range is read from HBM once (the other tiles hit L2).
+// Per item:
 //   * the 128 query rows are gathered straight from the fp16 query matrix into TENSOR
 //     MEMORY (tcgen05.st), where they stay as the A operand for the whole range
 //     (K = d <= 768 fp16 -> <= 384 TMEM columns); the queries are never re-streamed;
-//   * the bucket's rows stream HBM -> shared memory by TMA (64 rows x 128 B boxes,
-//     SWIZZLE_128B, ring of SCAN_STAGES x 8 KB) and are the B operand;
+//   * the bucket's rows stream HBM/L2 -> shared memory by TMA (64 rows x 128 B boxes,
+//     SWIZZLE_128B, 4 boxes = 32 KB per pipeline stage, ring of 6 stages) as the B operand;
 //   * tcgen05.mma kind::f16 (fp16 x fp16 -> fp32) M=128, N=64, K=16 accumulates a
-//     128 x 64 score tile in TMEM, double buffered (2 x 64 columns);
-//   * four epilogue warps read the tile (tcgen05.ld, thread == query row) and keep a
-//     threshold-gated sorted top-10 in registers; the score matrix never leaves the SM.
-// Roles: warps 0-3 epilogue (+ query gather), warp 4 TMA producer, warp 5 MMA issuer.
+//     128 x 64 score tile in TMEM, double buffered (2 x 64 columns).  MMA issue turned out
+//     to be synchronous with the tensor pipe, so two issuer warps alternate by tile and
+//     hide each other's barrier round trips;
+//   * eight epilogue warps read the tile (tcgen05.ld, thread == query row, warp == lane
+//     quarter x column half) and keep a threshold-gated sorted top-10 in registers; the
+//     score matrix never leaves the SM.
+// Roles: warps 0-7 epilogue (+ query gather), warp 8 TMA producer + item scheduler,
+// warps 9-10 MMA issuers.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -342,8 +349,8 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             // last accumulator tile before getting here)
             const int q = valid ? (pair_list[slot0 + row] / B) : 0;
             const uint4* qsrc = reinterpret_cast<const uint4*>(Q + (size_t)q * d);
-            for (int c = h; c < KB; c += 2) {
-                uint32_t r[32];
+            // two register buffers: the loads of k-block c + 2 are in flight while c is stored to TMEM
+            auto load_kblock = [&](uint32_t (&r)[32], int c) {
                 if (valid) {
 #pragma unroll
                     for (int v = 0; v < 8; ++v) {
@@ -357,7 +364,20 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
 #pragma unroll
                     for (int v = 0; v < 32; ++v) r[v] = 0u;
                 }
-                ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), r);
+            };
+            {
+                uint32_t ra[32], rb[32];
+                int c = h;
+                if (c < KB) load_kblock(ra, c);
+                while (c < KB) {
+                    if (c + 2 < KB) load_kblock(rb, c + 2);
+                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), ra);
+                    c += 2;
+                    if (c >= KB) break;
+                    if (c + 2 < KB) load_kblock(ra, c + 2);
+                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), rb);
+                    c += 2;
+                }
             }
             ptx::tmem_st_wait();
             *gate_mine = -INFINITY;
