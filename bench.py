@@ -511,8 +511,14 @@ def main():
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    long_region = total_ms >= 1000.0
-    tf_peak = float(peaks.get("bf16_tflops_sustained" if long_region else "bf16_tflops", 1590.0))
+    clocks = sampler.summary([win_dev, (t_a, t_b)])
+    # burst peak for a kernel timed alone, sustained for one timed inside a long step: the timed region
+    # is K back-to-back steps (the scan is ~90 % of each), so it counts as "long" when it lasts >= 1 s or
+    # the clock samples taken during it show the power cap engaged (cuBLAS at the burst figure does not)
+    long_region = total_ms >= 1000.0 or "sw_power_cap" in clocks.get("reasons", [])
+    tf_burst = float(peaks.get("bf16_tflops", 1590.0))
+    tf_sustained = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    tf_peak = tf_sustained if long_region else tf_burst
     counts = li.last_plan["counts"].cpu().numpy().astype(np.int64)
     sizes_local = w["local_sizes"].astype(np.int64)
     flops = 2.0 * D * float((counts * sizes_local).sum())
@@ -531,12 +537,14 @@ def main():
         roof = {"bound": "hbm", "achieved": bytes_alg / scan_s / 1e9, "peak": hbm_peak, "unit": "GB/s"}
     roof["frac"] = roof["achieved"] / roof["peak"]
     roof["traffic"] = traffic
+    if roof["bound"] == "tensor":
+        roof["frac_of_burst_peak"] = roof["achieved"] / tf_burst
+        roof["frac_of_sustained_peak"] = roof["achieved"] / tf_sustained
     roof.update(kernel="scan_topk_tc_kernel", launch_ms=scan_s * 1e3, alg_flops=flops, alg_bytes=bytes_alg,
                 hbm_gbs_achieved=bytes_alg / scan_s / 1e9, tflops_achieved=flops / scan_s / 1e12,
                 peak_source=("MEASURED_PEAKS.json" if peaks else "fallback") +
-                            (" (sustained)" if long_region and peaks else " (burst)" if peaks else ""))
-
-    clocks = sampler.summary([win_dev, (t_a, t_b)])
+                            (" (sustained: back-to-back steps, power cap engaged or >= 1 s)" if long_region and peaks
+                             else " (burst)" if peaks else ""))
 
     # ---- CPU baseline (rank 0, N == 1 only) ----
     cpu = None
