@@ -361,7 +361,24 @@ def pick_sample(t_probe, n_probe, nq, budget_s, runs):
 
 
 # --------------------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def emit_json(obj):
+    """The ONE line on the real stdout (libraries such as NCCL print banners to fd 1, which main() points at stderr)."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -586,7 +603,7 @@ def main():
         "clocks": clocks,
     }
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit_json(out)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -632,7 +649,7 @@ def run_reference(args, wl_name, rank, world, local_rank):
         "e2e": {"value": qps, "unit": "QPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out), flush=True)
+    emit_json(out)
 
 
 if __name__ == "__main__":
