@@ -584,11 +584,12 @@ def main():
         except Exception as e:  # the GPU numbers stand; say why the CPU leg is absent
             cpu = {"value": None, "unit": "QPS", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
 
-    launches_per_step = 2 + 1 + 3 + 1 + 1 + (1 if world > 1 else 0)  # linear x2, softmax_topn, invert x3, scan, merge(, rank merge)
+    # split_tf32 (queries), linear_tc x2, softmax_topn, invert x3, scan, merge(, rank merge)
+    launches_per_step = 1 + 2 + 1 + 3 + 1 + 1 + (1 if world > 1 else 0)
     out = {
         "metric": "QPS at recall@10>=0.90", "value": value, "unit": "QPS", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f16 in / f32 accumulate (scan), f32 (MLP)", "data": "synthetic",
+        "dtype": "f16 in / f32 accumulate (scan), tf32 x3 split / f32 accumulate (MLP)", "data": "synthetic",
         "config": {"workload": wl_name, "n": args.n, "nq": nq, "d": D, "n_buckets_in_index": C, "probed_buckets": B,
                    "k": K_NN, "recall_at_10": recall, "sharding": f"buckets over {world} GPU(s)",
                    "l2_policy": "inputs larger than L2 (bucket vectors %.1f GB per GPU, read once per step)"

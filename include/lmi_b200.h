@@ -7,7 +7,8 @@
  * Each entry point below replaces one of them (file:line relative to the
  * reference checkout):
  *
- *   lmi_linear / lmi_softmax_topn  <- NeuralNetwork.predict_proba
+ *   lmi_linear_tc (+ lmi_split_tf32) / lmi_linear / lmi_softmax_topn
+ *                                  <- NeuralNetwork.predict_proba
  *                                     search/li/model.py:226-241 (Linear/ReLU
  *                                     stack :29-79, softmax :238, topk :239) and
  *                                     the 1-level slice bucket_order = classes[:, :B]
@@ -65,6 +66,19 @@ const char *lmi_error_string(int code);
  * x_is_f16 != 0 (widened exactly, as data_X_to_torch does, model.py:102-105). */
 int lmi_linear(const void *x, int x_is_f16, const float *W, const float *b, float *y,
                int nq, int in_dim, int out_dim, int relu, void *stream);
+
+/* Tensor-core form of lmi_linear (tcgen05 kind::tf32, TMA-fed) on SPLIT operands: every fp32
+ * value v is passed as hi + mid + lo with each part exact in tf32 (lmi_split_tf32), all part
+ * products of weight >= 2^-22 are accumulated, K-blocks of 32 in the tensor core and across
+ * K-blocks in fp32 registers -- fp32-quality logits, as parity with model.py:232 needs.
+ * x_mid/x_lo (w_mid/w_lo) are both NULL when the operand is exact in one part (fp16 data).
+ * Output: fp32 y and/or the three parts of y (the next layer's x operand). in_dim % 4 == 0. */
+int lmi_split_tf32(const void *x, int x_is_f16, int64_t count, float *hi, float *mid, float *lo,
+                   void *stream);
+int lmi_linear_tc(const float *x_hi, const float *x_mid, const float *x_lo,
+                  const float *w_hi, const float *w_mid, const float *w_lo, const float *bias,
+                  int nq, int in_dim, int out_dim, int relu,
+                  float *y, float *y_hi, float *y_mid, float *y_lo, void *stream);
 
 /* softmax over the C logits of each row, then the B most probable classes in
  * descending probability (ties: lower class index first).

@@ -14,7 +14,7 @@ from ctypes import c_char_p, c_int, c_int64, c_void_p
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "liblmi_b200.so")
-SOURCES = ["lmi_mlp.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu"]
+SOURCES = ["lmi_mlp.cu", "lmi_mlp_tc.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
@@ -57,6 +57,9 @@ _SIGNATURES = {
     "lmi_version": (c_int, []),
     "lmi_error_string": (c_char_p, [c_int]),
     "lmi_linear": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "lmi_split_tf32": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "lmi_linear_tc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                              c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lmi_softmax_topn": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "lmi_argmax": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "lmi_scatter_rows": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_void_p, c_void_p]),

@@ -3,10 +3,11 @@
 //   lmi_softmax_topn  softmax + top-B classes          (model.py:238-239; LearnedIndex.py:209-214)
 //   lmi_argmax        first maximum per row            (model.py:223)
 //
-// fp32 FMA on purpose: parity demands probed-bucket lists identical to the reference's
-// fp32 torch path except where probabilities tie within 1e-6; a single-pass fp16/tf32
-// tensor-core product perturbs logits by ~1e-3 relative and flips ranks far above that.
-// The whole network is 9.1 GFLOP at 10k queries -- a few percent of the scan.
+// lmi_linear is the fp32 CUDA-core form of a Linear layer: the verification kernel for the
+// tensor-core path (lmi_mlp_tc.cu, split-precision tcgen05) and the fallback for input
+// widths that are not a multiple of 4.  Parity demands probed-bucket lists identical to the
+// reference's fp32 torch path except where probabilities tie within 1e-6, so both keep
+// fp32 quality; a single-pass fp16/tf32 product would perturb logits by ~1e-3 relative.
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <float.h>

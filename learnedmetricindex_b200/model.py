@@ -8,6 +8,7 @@ behind ``lmi_linear`` / ``lmi_softmax_topn`` / ``lmi_argmax``.  Training
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -70,6 +71,10 @@ class NeuralNetwork:
             assert W1.shape[1] == W0.shape[0], "layer shapes do not chain"
         self.input_dim = self.layers[0][0].shape[1]
         self.n_output_neurons = self.layers[-1][0].shape[0]
+        # "tc": tcgen05 tf32 split-precision GEMM (product path); "ffma": fp32 CUDA-core kernel
+        # (verification, and the fallback for input widths that are not a multiple of 4)
+        self.impl = os.environ.get("LMI_MLP_IMPL", "tc")
+        self._w_parts: Optional[List[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]] = None
 
     # -- construction from the reference's objects ------------------------------------
     @classmethod
@@ -88,12 +93,47 @@ class NeuralNetwork:
         return cls(layers, device=device)
 
     # -- kernels ----------------------------------------------------------------------
+    def _split(self, t: torch.Tensor, exact_in_one_part: bool):
+        """hi/mid/lo tf32 parts of a device tensor (``lmi_split_tf32``)."""
+        L = _native.lib()
+        hi = torch.empty(t.shape, dtype=torch.float32, device=self.device)
+        mid = lo = None
+        if not exact_in_one_part:
+            mid, lo = torch.empty_like(hi), torch.empty_like(hi)
+        _native.check(L.lmi_split_tf32(t.data_ptr(), int(t.dtype == torch.float16), t.numel(), hi.data_ptr(),
+                                       mid.data_ptr() if mid is not None else None,
+                                       lo.data_ptr() if lo is not None else None, _stream_ptr()), "lmi_split_tf32")
+        return hi, mid, lo
+
+    def _tc_ok(self) -> bool:
+        return self.impl == "tc" and all(W.shape[1] % 4 == 0 for W, _ in self.layers)
+
     def logits(self, x: torch.Tensor) -> torch.Tensor:
         """``Model.forward`` (model.py:97-99) on a device matrix (fp16 or f32)."""
         L = _native.lib()
         assert x.is_cuda and x.dim() == 2 and x.is_contiguous()
         assert x.shape[1] == self.input_dim, (x.shape, self.input_dim)
         nq = x.shape[0]
+        if nq > 0 and self._tc_ok():
+            if self._w_parts is None:
+                self._w_parts = [self._split(W, False) for W, _ in self.layers]
+            ptr = lambda t: t.data_ptr() if t is not None else None
+            parts = self._split(x, x.dtype == torch.float16)  # fp16 values are exact in one tf32 part
+            out = None
+            for li, ((W, b), wp) in enumerate(zip(self.layers, self._w_parts)):
+                last = li + 1 == len(self.layers)
+                shape = (nq, W.shape[0])
+                if last:
+                    out = torch.empty(shape, dtype=torch.float32, device=self.device)
+                    nxt = (None, None, None)
+                else:
+                    nxt = tuple(torch.empty(shape, dtype=torch.float32, device=self.device) for _ in range(3))
+                _native.check(L.lmi_linear_tc(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), ptr(wp[0]), ptr(wp[1]),
+                                              ptr(wp[2]), b.data_ptr(), nq, W.shape[1], W.shape[0], int(not last),
+                                              ptr(out) if last else None, ptr(nxt[0]), ptr(nxt[1]), ptr(nxt[2]),
+                                              _stream_ptr()), "lmi_linear_tc")
+                parts = nxt
+            return out
         h = x
         for li, (W, b) in enumerate(self.layers):
             out = torch.empty((nq, W.shape[0]), dtype=torch.float32, device=self.device)

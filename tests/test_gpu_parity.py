@@ -36,10 +36,12 @@ def _order_rows_equal(got, exp, probs, tol=1e-6):
 
 
 @pytest.mark.parametrize("name", case_names())
-def test_mlp_matches_reference_golden(name):
+@pytest.mark.parametrize("mlp_impl", ["tc", "ffma"])
+def test_mlp_matches_reference_golden(name, mlp_impl):
     c = GoldenCase(name)
     C = c.n_categories[0]
     li = _index(c.layers, C)
+    li.root_model.impl = mlp_impl  # "tc": tcgen05 tf32 split GEMM (product path); "ffma": fp32 CUDA-core kernel
     probs, classes = li.root_model.predict_proba(c.Q)
     assert probs.dtype == np.float32 and classes.dtype == np.int64 and classes.shape == c.classes.shape
     np.testing.assert_allclose(probs, c.probs, rtol=2e-5, atol=1e-7)
@@ -48,6 +50,33 @@ def test_mlp_matches_reference_golden(name):
     pred = li.root_model.predict(c.X)
     exp = orc.predict(c.layers, orc.to_f32_tensor(c.X))
     assert (pred == exp).mean() > 0.999
+
+
+def test_mlp_tensor_core_logits_have_fp32_quality():
+    """The split-precision tcgen05 Linear layers against a float64 evaluation: the error must be of
+    the order of an fp32 evaluation's own (here: not worse than the CUDA-core fp32 kernel's by 2x),
+    for fp16 and f32 inputs, incl. widths that are not multiples of the tile sizes."""
+    from learnedmetricindex_b200 import NeuralNetwork
+
+    rs = np.random.RandomState(3)
+    for nq, d, H, C in [(1000, 768, 512, 120), (130, 100, 72, 10), (1, 64, 8, 3), (257, 96, 128, 65)]:
+        layers = [(rs.randn(H, d).astype(np.float32) / np.sqrt(d), rs.randn(H).astype(np.float32) * 0.1),
+                  (rs.randn(C, H).astype(np.float32) / np.sqrt(H), rs.randn(C).astype(np.float32) * 0.1)]
+        x = rs.randn(nq, d).astype(np.float32)
+        for xq in (x.astype(np.float16), x):
+            h = xq.astype(np.float64)
+            for li_, (W, b) in enumerate(layers):
+                h = h @ W.astype(np.float64).T + b.astype(np.float64)
+                if li_ == 0:
+                    h = np.maximum(h, 0)
+            errs = {}
+            for impl in ("tc", "ffma"):
+                net = NeuralNetwork(layers)
+                net.impl = impl
+                out = net.logits(torch.from_numpy(xq).cuda()).cpu().numpy().astype(np.float64)
+                errs[impl] = np.abs(out - h).max()
+            scale = np.abs(h).max()
+            assert errs["tc"] <= max(2 * errs["ffma"], 4e-7 * scale), (nq, d, H, C, xq.dtype, errs, scale)
 
 
 def test_invert_matches_numpy():
