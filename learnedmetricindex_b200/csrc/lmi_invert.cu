@@ -89,17 +89,31 @@ invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __re
         carry_items = 0;
     }
     __syncthreads();
+    // column scan of the per-chunk histograms: one warp per bucket, 32 chunks per trip (independent
+    // loads), exclusive scan across the lanes; the bucket totals land in shared memory
+    for (int c = threadIdx.x >> 5; c < C; c += (int)(blockDim.x >> 5)) {
+        const int lane = threadIdx.x & 31;
+        int run = 0;
+        for (int g0 = 0; g0 < G; g0 += 32) {
+            const int g = g0 + lane;
+            const int t = (g < G) ? hist[(size_t)g * C + c] : 0;
+            int incl = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += u;
+            }
+            if (g < G) hist[(size_t)g * C + c] = run + incl - t;
+            run += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) counts[c] = run;
+    }
+    __threadfence_block();
+    __syncthreads();
     for (int c0 = 0; c0 < C; c0 += blockDim.x) {
         const int c = c0 + threadIdx.x;
         int m = 0;
-        if (c < C) {
-            for (int g = 0; g < G; ++g) {
-                const int t = hist[(size_t)g * C + c];
-                hist[(size_t)g * C + c] = m;
-                m += t;
-            }
-            counts[c] = m;
-        }
+        if (c < C) m = counts[c];
         int tot_pairs;
         const int off = block_exclusive_scan(m, warp_tot, tot_pairs) + carry_pairs;
         if (c < C) offsets[c] = off;

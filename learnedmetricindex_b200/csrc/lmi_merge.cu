@@ -68,6 +68,57 @@ __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int3
         }
         const int nl = min(bucket_lists[b], lmax);
         const int slot = slot_of_pair[p];
+        if (nl <= 32) {
+            // common case: one list per lane, held entirely in registers; the winner's list shifts down
+            const size_t lbase = ((size_t)slot * lmax + lane) * MK;
+            float ls[MK];
+            int lr[MK];
+#pragma unroll
+            for (int t = 0; t < MK; t += 2) {
+                float2 sv = make_float2(-INFINITY, -INFINITY);
+                int2 rv = make_int2(-1, -1);
+                if (lane < nl) {
+                    sv = *reinterpret_cast<const float2*>(part_sim + lbase + t);
+                    rv = *reinterpret_cast<const int2*>(part_row + lbase + t);
+                }
+                ls[t] = sv.x;
+                ls[t + 1] = sv.y;
+                lr[t] = rv.x;
+                lr[t + 1] = rv.y;
+            }
+            float res_d = 0.f;
+            int res_row = 0x7fffffff;
+#pragma unroll 1
+            for (int t = 0; t < MK; ++t) {
+                float wd = (lr[0] >= 0) ? -ls[0] : INFINITY;
+                int wrow = (lr[0] >= 0) ? lr[0] : 0x7fffffff;
+                warp_argmin(wd, wrow);
+                if (lane == t) {
+                    res_d = wd;
+                    res_row = wrow;
+                }
+                if (wrow != 0x7fffffff && lr[0] == wrow) {
+#pragma unroll
+                    for (int u = 0; u + 1 < MK; ++u) {
+                        ls[u] = ls[u + 1];
+                        lr[u] = lr[u + 1];
+                    }
+                    lr[MK - 1] = -1;
+                }
+            }
+            if (lane < MK) {
+                if (res_row == 0x7fffffff) {
+                    // fewer than 10 objects: faiss pads with I = -1 / D = -FLT_MAX, the reference maps
+                    // -1 to the bucket's last label and 1 - (-FLT_MAX) to FLT_MAX (:368-370)
+                    e_dist[r * MK + lane] = 1.0f - (-FLT_MAX);
+                    e_id[r * MK + lane] = ids[hi - 1];
+                } else {
+                    e_dist[r * MK + lane] = 1.0f + res_d;
+                    e_id[r * MK + lane] = ids[res_row];
+                }
+            }
+            continue;
+        }
         // lane walks the (descending) lists lane, lane+32, ...; a taken head is replaced by the
         // list's next entry
         const size_t base = (size_t)slot * lmax * MK;

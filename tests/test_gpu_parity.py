@@ -191,6 +191,21 @@ def test_search_matches_oracle_medium(impl):
     assert abs(r_gpu - r_cpu) <= 1e-3, (r_gpu, r_cpu)  # recall@10 identical within 0.1 pp
 
 
+def test_many_ranges_per_bucket(monkeypatch):
+    """Short ranges over large buckets: > 32 partial lists per (query, bucket) take the merge
+    kernel's strided-list path, and sibling query tiles share ranges under the dynamic scheduler."""
+    monkeypatch.setenv("LMI_RANGE_ROWS", "1024")
+    n, nq, C, B = 120_000, 700, 4, 2
+    X, Q, layers, pred = _synthetic(n, nq, C, steps=40)
+    li = _index(layers, C)
+    d, i, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=B, k=10)
+    assert li.last_plan["rmax"] > 16
+    exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=10)
+    same = (li.last_bucket_order.cpu().numpy() == exp_order[:, :, 0]).all(axis=1)
+    assert same.mean() > 0.99
+    assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what="many ranges")
+
+
 def test_f32_queries_and_float_inputs():
     """f32 host inputs (the reference's documented dtype) take the cast path."""
     n, nq, C, B = 8000, 300, 8, 2
