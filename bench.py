@@ -216,7 +216,8 @@ def build_workload(args, device, rank, world, use_repo_kernels=True):
 
     from learnedmetricindex_b200.sharded import owner_of_bucket, partition_buckets
 
-    parts = partition_buckets(sizes_h, world)
+    # queries follow the data distribution, so a bucket's scan work (probes x rows) goes like size^2
+    parts = partition_buckets(sizes_h, world, weights=sizes_h)
     own = torch.from_numpy(owner_of_bucket(parts, C)).to(device)
     local_sizes = np.where(owner_of_bucket(parts, C) == rank, sizes_h, 0)
     off = np.zeros(C + 1, dtype=np.int64)

@@ -137,7 +137,7 @@ class LearnedIndex:
 
     # ------------------------------------------------------------------ search ------
     def search_device(self, qn: torch.Tensor, qs: torch.Tensor, n_categories: List[int], n_buckets: int, k: int,
-                      events=None, out=None):
+                      events=None, out=None, bucket_order: Optional[torch.Tensor] = None):
         """Everything between the H2D and D2H copies.  ``qn`` / ``qs``: device matrices
         (fp16 or f32).  Returns device tensors (dists f64[nq,k'], nns int32-bits[nq,k']);
         ``out=(dists, nns)`` supplies them (e.g. views into an all-gather send buffer)."""
@@ -156,8 +156,12 @@ class LearnedIndex:
             if events is not None:
                 events[i].record()
 
-        mark(0)
-        order, probs = self._bucket_order_device(qn, B, n_categories)
+        if bucket_order is None:
+            mark(0)
+            order, probs = self._bucket_order_device(qn, B, n_categories)
+        else:  # computed elsewhere (query-sharded navigation of the multi-GPU path); events[0] is the caller's
+            order, probs = bucket_order, None
+            assert order.shape == (nq, B) and order.dtype == torch.int32 and order.is_contiguous()
         self.last_bucket_order, self.last_probs = order, probs
         mark(1)
 

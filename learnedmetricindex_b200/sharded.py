@@ -104,6 +104,28 @@ def gather_and_merge(buf: GatherBuffers, group=None,
     return out_d, out_i
 
 
+def query_slice(nq: int, world: int, rank: int) -> Tuple[int, int, int]:
+    """(start, stop, padded slice length) of the queries whose bucket order ``rank`` computes."""
+    per = -(-nq // world) if nq else 0
+    start = min(nq, rank * per)
+    return start, min(nq, start + per), per
+
+
+def gather_bucket_order(order_local: torch.Tensor, nq: int, n_probe: int, group=None) -> torch.Tensor:
+    """The navigation step sharded by queries: every rank runs the MLP + top-B on its slice only
+    and the int32 ``[slice, B]`` results are all-gathered (``nq*B*4`` bytes in total; 160 KB at
+    10k x 4) -- every rank needs the whole bucket order to find the probes of its own buckets."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    start, stop, per = query_slice(nq, world, rank)
+    send = torch.full((per, n_probe), -1, dtype=torch.int32, device=order_local.device)
+    if stop > start:
+        send[: stop - start] = order_local
+    recv = torch.empty((world * per, n_probe), dtype=torch.int32, device=order_local.device)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    return recv[:nq].contiguous()
+
+
 class ShardedLearnedIndex:
     """``LearnedIndex`` whose buckets are spread over the ranks of ``group``.
 
@@ -111,9 +133,10 @@ class ShardedLearnedIndex:
     owns (``DeviceBucketLayout.restrict_to_buckets`` or a layout built from the local rows).
     """
 
-    def __init__(self, local, group=None):
+    def __init__(self, local, group=None, shard_navigation: bool = True):
         self.local = local
         self.group = group
+        self.shard_navigation = shard_navigation  # MLP + top-B on nq/world queries per rank, then all-gather
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self._bufs = {}
@@ -130,8 +153,32 @@ class ShardedLearnedIndex:
         nq = qs.shape[0]
         k_out = PER_BUCKET_K if int(n_buckets) == 1 else int(k)
         buf = self._buffers(nq, k_out, qs.device)
-        self.local.search_device(qn, qs, n_categories, n_buckets, k, events=events, out=buf.local_views())
+        order = None
+        if self.shard_navigation and self.world > 1 and nq >= self.world:
+            if events is not None:
+                events[0].record()
+            start, stop, _ = query_slice(nq, self.world, self.rank)
+            local_order, _ = self.local._bucket_order_device(qn[start:stop], int(n_buckets), list(n_categories))
+            order = gather_bucket_order(local_order, nq, int(n_buckets), self.group)
+        self.local.search_device(qn, qs, n_categories, n_buckets, k, events=events, out=buf.local_views(),
+                                 bucket_order=order)
         return gather_and_merge(buf, self.group)
+
+    def _upload_sharded(self, host_matrix, dev) -> torch.Tensor:
+        """Host queries -> device on every rank: each rank copies only its 1/world slice over PCIe and
+        the slices are all-gathered over NVLink (every rank is handed the same host batch)."""
+        from .model import to_device_matrix
+
+        nq = len(host_matrix)
+        if self.world == 1 or nq < self.world:
+            return to_device_matrix(host_matrix, dev)
+        start, stop, per = query_slice(nq, self.world, self.rank)
+        part = to_device_matrix(host_matrix[start:stop], dev)
+        send = torch.zeros((per, part.shape[1]), dtype=part.dtype, device=dev)
+        send[: stop - start] = part
+        recv = torch.empty((self.world * per, part.shape[1]), dtype=part.dtype, device=dev)
+        dist.all_gather_into_tensor(recv, send, group=self.group)
+        return recv[:nq]
 
     def search(self, data_navigation, queries_navigation, data_search, queries_search, data_prediction,
                n_categories, n_buckets: int = 1, k: int = 10):
@@ -144,8 +191,8 @@ class ShardedLearnedIndex:
 
         t0 = time.time()
         dev = self.local.device
-        qn = to_device_matrix(queries_navigation, dev)
-        qs = qn if queries_search is queries_navigation else to_device_matrix(queries_search, dev)
+        qn = self._upload_sharded(queries_navigation, dev)
+        qs = qn if queries_search is queries_navigation else self._upload_sharded(queries_search, dev)
         d, i = self.search_device(qn, qs, list(n_categories), n_buckets, k)
         dists = d.cpu().numpy()
         nns = i.cpu().numpy().view(np.uint32)

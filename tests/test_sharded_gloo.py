@@ -127,3 +127,39 @@ def test_sharded_search_world2_gloo(B, k):
             assert_search_parity(np.where(real, d, exp_d), np.where(real, i, exp_i), exp_d, exp_i, what=f"rank {r}")
     np.testing.assert_array_equal(ret[0][0], ret[1][0])
     np.testing.assert_array_equal(ret[0][1], ret[1][1])
+
+
+def _order_worker(rank, world, port, nq, B, ret):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from learnedmetricindex_b200.sharded import gather_bucket_order, query_slice
+
+        full = torch.arange(nq * B, dtype=torch.int32).reshape(nq, B) % 17
+        start, stop, per = query_slice(nq, world, rank)
+        got = gather_bucket_order(full[start:stop].contiguous(), nq, B)
+        ret[rank] = got.numpy().copy()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("nq,B", [(97, 3), (2, 1), (64, 4)])
+def test_query_sharded_navigation_gathers_full_order(nq, B):
+    """Each rank contributes the bucket order of its query slice; every rank ends up with all of it."""
+    from learnedmetricindex_b200.sharded import query_slice
+
+    world = 2
+    covered = []
+    for r in range(world):
+        a, b, per = query_slice(nq, world, r)
+        covered += list(range(a, b))
+        assert b - a <= per
+    assert covered == list(range(nq))
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_order_worker, args=(world, _free_port(), nq, B, ret), nprocs=world, join=True)
+    full = (np.arange(nq * B, dtype=np.int32).reshape(nq, B) % 17)
+    for r in range(world):
+        np.testing.assert_array_equal(ret[r], full)
