@@ -14,6 +14,11 @@
  *                                     the 1-level slice bucket_order = classes[:, :B]
  *                                     search/li/LearnedIndex.py:209-214
  *   lmi_argmax                     <- NeuralNetwork.predict  search/li/model.py:213-224
+ *   lmi_softmax_probs / lmi_navigate_tree
+ *                                  <- the multi-level branch of _precompute_bucket_order
+ *                                     search/li/LearnedIndex.py:216-252 with
+ *                                     _visit_internal_nodes :254-301, _visit_buckets
+ *                                     :303-325 and PriorityQueue (search/li/PriorityQueue.py:7-94)
  *   lmi_invert                     <- filter_path_idxs       search/li/utils.py:61-65,
  *                                     as called per bucket per round at
  *                                     search/li/LearnedIndex.py:353
@@ -47,7 +52,7 @@
 extern "C" {
 #endif
 
-#define LMI_B200_ABI_VERSION 2
+#define LMI_B200_ABI_VERSION 3
 
 #define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
 #define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
@@ -88,6 +93,28 @@ int lmi_softmax_topn(const float *logits, int nq, int C, int B,
 
 /* argmax over the C logits of each row (first maximum), int64 out. */
 int lmi_argmax(const float *logits, int64_t n, int C, int64_t *out, void *stream);
+
+/* ---- multi-level navigation (n_levels > 1) --------------------------------------
+ * Tree nodes are numbered breadth first: depth-1 nodes 0..C1-1 (node id == class of the root
+ * model), then every depth-2 node parent-major, and so on; the children of a node are
+ * contiguous.  node_prob[q, v] is the probability the model of v's PARENT gives v's class for
+ * query q (raw, not multiplied by the parent's own probability -- LearnedIndex.py:295-299). */
+
+/* probs[q*out_stride + out_col0 + c] = softmax(logits[q, :])[c]  (model.py:238), C columns. */
+int lmi_softmax_probs(const float *logits, int nq, int C, float *probs, int64_t out_stride,
+                      int64_t out_col0, void *stream);
+
+/* Per query: best-first search over the tree.  The frontier starts as the n_roots depth-1
+ * nodes; the most probable frontier node is popped (ties: lowest node id; the reference's
+ * unstable argsort leaves ties undefined, PriorityQueue.py:80); a popped node with
+ * n_children[v] > 0 (it has an internal model) opens children first_child[v] .. +n_children[v];
+ * a popped node with node_bucket[v] >= 0 (its path is in bucket_paths) appends that flat
+ * bucket id to the query's order; a node that is neither is dropped, as in the reference.
+ * Stops after B buckets.  bucket_order int32[nq,B]; -1 where the tree ran out (the host
+ * rejects budgets beyond the reachable buckets before launching). */
+int lmi_navigate_tree(const float *node_prob, int nq, int n_nodes, const int32_t *first_child,
+                      const int32_t *n_children, const int32_t *node_bucket, int n_roots, int B,
+                      int32_t *bucket_order, void *stream);
 
 /* ---- bucket layout ------------------------------------------------------------ */
 

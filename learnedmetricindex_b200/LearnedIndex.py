@@ -27,6 +27,7 @@ import torch
 from . import _native
 from .layout import DeviceBucketLayout
 from .model import NeuralNetwork, to_device_matrix
+from .navigation import NavigationTree, flat_bucket_ids, unflatten_bucket_ids
 
 EMPTY_VALUE = -1  # search/li/PriorityQueue.py:4
 PER_BUCKET_K = 10  # `k` is not forwarded to _search_single_bucket (LearnedIndex.py:111-117, :334)
@@ -81,6 +82,7 @@ class LearnedIndex:
         self._layout_refs = None
         self.last_bucket_order: Optional[torch.Tensor] = None
         self.last_probs: Optional[torch.Tensor] = None
+        self._tree: Optional[NavigationTree] = None
         self._n_sms = torch.cuda.get_device_properties(self.device).multi_processor_count
 
     @classmethod
@@ -103,23 +105,37 @@ class LearnedIndex:
         pred = np.asarray(data_prediction)
         if pred.ndim == 1:
             pred = pred[:, None]
-        if len(n_categories) != 1:
-            raise NotImplementedError("multi-level indexes: see DESIGN.md (next row of SURVEY §8f)")
+        assert pred.shape[1] == len(n_categories), "data_prediction columns != levels"
+        if len(n_categories) == 1:
+            labels, n_layout_buckets = pred[:, 0], int(n_categories[0])
+        else:
+            # groupby(category_L1..L) key order == mixed-radix flat id (:343-350); rows whose path is
+            # incomplete (EMPTY_VALUE) land in one trailing bucket no query can probe
+            labels = flat_bucket_ids(pred, n_categories)
+            n_layout_buckets = int(np.prod(n_categories))
+            if (labels == n_layout_buckets).any():
+                n_layout_buckets += 1
         ids = None
         if data_navigation is not None and hasattr(data_navigation, "index"):
             ids = np.asarray(data_navigation.index)
             if hasattr(data_search, "index") and not data_search.index.equals(data_navigation.index):
                 data_search = data_search.loc[data_navigation.index]  # label lookup, as :357 does
-        self._layout = DeviceBucketLayout.from_host(data_search, pred[:, 0], int(n_categories[0]), ids=ids,
+        self._layout = DeviceBucketLayout.from_host(data_search, labels, n_layout_buckets, ids=ids,
                                                     device=self.device)
         self._layout_key = key
         self._layout_refs = (data_search, data_prediction)  # keep ids from being recycled
         return self._layout
 
     # ------------------------------------------------------------------ navigation --
+    def navigation_tree(self, n_categories: List[int]) -> NavigationTree:
+        if self._tree is None or self._tree.n_categories != [int(c) for c in n_categories]:
+            self._tree = NavigationTree(self.root_model, self.internal_models, self.bucket_paths, n_categories)
+        return self._tree
+
     def _bucket_order_device(self, qn: torch.Tensor, n_buckets: int, n_categories: List[int]):
+        """(bucket ids int32[nq, n_buckets] -- flat ids for a multi-level index --, probabilities)."""
         if len(n_categories) != 1:
-            raise NotImplementedError("multi-level indexes: see DESIGN.md (next row of SURVEY §8f)")
+            return self.navigation_tree(n_categories).bucket_order(qn, n_buckets)
         C = self.root_model.n_output_neurons
         if n_buckets > C:
             raise ValueError(f"n_buckets={n_buckets} exceeds the {C} buckets of the index")
@@ -133,7 +149,10 @@ class LearnedIndex:
         order, _ = self._bucket_order_device(qn, n_buckets, list(n_categories))
         e1.record()
         e1.synchronize()
-        return order.cpu().numpy().reshape(qn.shape[0], n_buckets, 1), e0.elapsed_time(e1) / 1e3
+        order = order.cpu().numpy()
+        if len(n_categories) == 1:
+            return order.reshape(qn.shape[0], n_buckets, 1), e0.elapsed_time(e1) / 1e3
+        return unflatten_bucket_ids(order, n_categories), e0.elapsed_time(e1) / 1e3
 
     # ------------------------------------------------------------------ search ------
     def search_device(self, qn: torch.Tensor, qs: torch.Tensor, n_categories: List[int], n_buckets: int, k: int,

@@ -14,7 +14,7 @@ from ctypes import c_char_p, c_int, c_int64, c_void_p
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "liblmi_b200.so")
-SOURCES = ["lmi_mlp.cu", "lmi_mlp_tc.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu"]
+SOURCES = ["lmi_mlp.cu", "lmi_mlp_tc.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu", "lmi_navigate.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
@@ -62,6 +62,9 @@ _SIGNATURES = {
                               c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lmi_softmax_topn": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "lmi_argmax": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
+    "lmi_softmax_probs": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p]),
+    "lmi_navigate_tree": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p,
+                                  c_void_p]),
     "lmi_scatter_rows": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "lmi_cast_f16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "lmi_max_items": (c_int64, [c_int, c_int, c_int, c_int]),

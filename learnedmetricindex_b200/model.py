@@ -108,7 +108,14 @@ class NeuralNetwork:
     def _tc_ok(self) -> bool:
         return self.impl == "tc" and all(W.shape[1] % 4 == 0 for W, _ in self.layers)
 
-    def logits(self, x: torch.Tensor) -> torch.Tensor:
+    def split_input(self, x: torch.Tensor):
+        """The tf32 parts of a query matrix for ``logits(x, parts=...)`` -- shared by every model of
+        a multi-level index (None when this model runs the FFMA kernel)."""
+        if x.shape[0] == 0 or not self._tc_ok():
+            return None
+        return self._split(x, x.dtype == torch.float16)  # fp16 values are exact in one tf32 part
+
+    def logits(self, x: torch.Tensor, parts=None) -> torch.Tensor:
         """``Model.forward`` (model.py:97-99) on a device matrix (fp16 or f32)."""
         L = _native.lib()
         assert x.is_cuda and x.dim() == 2 and x.is_contiguous()
@@ -118,7 +125,8 @@ class NeuralNetwork:
             if self._w_parts is None:
                 self._w_parts = [self._split(W, False) for W, _ in self.layers]
             ptr = lambda t: t.data_ptr() if t is not None else None
-            parts = self._split(x, x.dtype == torch.float16)  # fp16 values are exact in one tf32 part
+            if parts is None:
+                parts = self.split_input(x)
             out = None
             for li, ((W, b), wp) in enumerate(zip(self.layers, self._w_parts)):
                 last = li + 1 == len(self.layers)

@@ -24,7 +24,36 @@ def seeded_layers(seed, model_type, in_dim, out_dim, scale=1.0):
 
 
 def case_names():
-    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+    """1-level fixtures."""
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "l1_*.npz")))
+
+
+def multi_level_case_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "ml_*.npz")))
+
+
+class MultiLevelCase:
+    """``ml_*.npz`` (oracle/make_golden.py:multi_level_case): weights are regenerated from the seeds."""
+
+    def __init__(self, name):
+        z = np.load(os.path.join(GOLDEN_DIR, f"{name}.npz"))
+        self.name, self.z = name, z
+        self.X, self.Q = z["X"], z["Q"]
+        self.data_prediction, self.ids = z["data_prediction"], z["ids"]
+        self.n_categories = [int(v) for v in z["n_categories"]]
+        L = len(self.n_categories)
+        d = self.X.shape[1]
+        scale = float(z["weight_scale"])
+        self.root_layers = seeded_layers(int(z["root_seed"]), str(z["root_type"]), d, self.n_categories[0], scale)
+        self.internal = {}
+        for row in z["internal_meta"]:
+            path = tuple(int(v) for v in row[:L])
+            self.internal[path] = seeded_layers(int(row[L]), str(z["inner_type"]), d, int(row[L + 1]), scale)
+        self.bucket_paths = [tuple(int(v) for v in r) for r in z["bucket_paths"]]
+        self.runs = [(int(b), int(k)) for b, k in z["runs"]]
+
+    def expected(self, B, k):
+        return self.z[f"order_B{B}_k{k}"], self.z[f"dists_B{B}_k{k}"], self.z[f"nns_B{B}_k{k}"]
 
 
 class GoldenCase:

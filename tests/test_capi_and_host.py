@@ -24,7 +24,7 @@ def test_library_builds_loads_and_exports_header_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/lmi_b200.h but not exported"
     assert set(declared) == set(_native.EXPORTED_SYMBOLS), "ctypes signatures out of sync with the header"
-    assert lib.lmi_version() == 2
+    assert lib.lmi_version() == 3
     assert lib.lmi_error_string(0) == b"success"
     assert b"bad argument" in lib.lmi_error_string(-1)
     # size helpers are pure host functions
@@ -93,3 +93,18 @@ def test_plan_scan(nq, B, C, n, maxb):
     assert 1 <= rmax <= MAX_RANGES
     assert rmax * length >= maxb  # every bucket is covered
     assert (rmax - 1) * length < maxb or rmax == 1
+
+
+def test_flat_bucket_ids_follow_groupby_key_order():
+    """Multi-level layout: flat id == rank of the path in groupby(category_L1..L) key order
+    (LearnedIndex.py:343-350); incomplete paths go to one trailing, unprobeable bucket."""
+    from learnedmetricindex_b200.navigation import flat_bucket_ids, unflatten_bucket_ids
+
+    cats = [3, 4, 2]
+    paths = np.array([[a, b, c] for a in range(3) for b in range(4) for c in range(2)])
+    flat = flat_bucket_ids(paths, cats)
+    assert np.array_equal(flat, np.arange(24))  # lexicographic == ascending flat id
+    assert np.array_equal(unflatten_bucket_ids(flat, cats), paths)
+    bad = np.array([[0, -1, -1], [2, 3, 1], [3, 0, 0], [1, 4, 0]])
+    assert flat_bucket_ids(bad, cats).tolist() == [24, 23, 24, 24]
+    assert unflatten_bucket_ids(np.array([[5, -1]]), cats).tolist() == [[[0, 2, 1], [-1, -1, -1]]]

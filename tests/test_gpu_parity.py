@@ -10,7 +10,8 @@ import pytest
 import torch
 
 from oracle import lmi_oracle as orc
-from tests.golden_util import GoldenCase, assert_search_parity, case_names
+from tests.golden_util import (GoldenCase, MultiLevelCase, assert_search_parity, case_names,
+                               multi_level_case_names)
 
 pytestmark = pytest.mark.gpu
 
@@ -264,3 +265,85 @@ def test_errors():
     assert d.shape == (nq, 10)  # `k` is not forwarded when n_buckets == 1 (LearnedIndex.py:111-117)
     d, i, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=3, k=20)
     assert d.shape == (nq, 20)
+
+
+# ----------------------------------------------------------------------------- multi-level
+def _oracle_node_probs(root_layers, internal, Q):
+    """Every probability the reference's queue can hold for a query (root + all internal models),
+    unsorted, f32[nq, total classes] -- to decide whether a differing visit order is a tie."""
+    cols = []
+    for layers in [root_layers] + list(internal.values()):
+        p, cls = orc.predict_proba(layers, orc.to_f32_tensor(Q))
+        cols.append(p)
+    return np.concatenate(cols, axis=1)
+
+
+def _multi_level_rows_equal(got_paths, exp_paths, node_probs, tol=1e-6):
+    same = (got_paths == exp_paths).all(axis=(1, 2))
+    for r in np.flatnonzero(~same):
+        p = np.sort(node_probs[r])
+        assert np.diff(p).min() <= tol, f"row {r}: visit order differs without a probability tie"
+    return same
+
+
+@pytest.mark.parametrize("name", multi_level_case_names())
+@pytest.mark.parametrize("mlp_impl", ["tc", "ffma"])
+def test_multi_level_matches_reference_golden(name, mlp_impl, monkeypatch):
+    """n_levels > 1 (LearnedIndex.py:216-325): dense grouped inference + lmi_navigate_tree against
+    what the reference's PriorityQueue search returned, then the unchanged scan/merge."""
+    import pandas as pd
+    from learnedmetricindex_b200 import LearnedIndex
+
+    monkeypatch.setenv("LMI_MLP_IMPL", mlp_impl)
+    c = MultiLevelCase(name)
+    li = LearnedIndex(c.root_layers, c.internal, c.bucket_paths)
+    assert li.root_model.impl == mlp_impl
+    df_nav = pd.DataFrame(c.X, index=pd.Index(c.ids))
+    df_search = pd.DataFrame(c.X, index=pd.Index(c.ids))
+    node_probs = _oracle_node_probs(c.root_layers, c.internal, c.Q)
+    for B, k in c.runs:
+        exp_order, exp_d, exp_i = c.expected(B, k)
+        got_paths, t_inf = li._precompute_bucket_order(c.Q, B, c.n_categories)
+        assert got_paths.dtype == np.int32 and got_paths.shape == exp_order.shape and t_inf >= 0
+        same = _multi_level_rows_equal(got_paths, exp_order, node_probs)
+        assert same.mean() > 0.98
+        d, i, times = li.search(df_nav, c.Q, df_search, c.Q, c.data_prediction, c.n_categories, n_buckets=B, k=k)
+        assert d.dtype == np.float64 and i.dtype == np.uint32
+        assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what=f"{name} B={B} k={k}")
+
+
+def test_multi_level_medium_matches_oracle():
+    """Two levels at a realistic width ([10, 10], the reference CLI default, search/search.py:314)
+    with separate navigation (48-d) and search (768-d) representations (search.py:192-216)."""
+    from learnedmetricindex_b200 import LearnedIndex
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(21)
+    n, nq, d_nav, d_search, cats, B = 40_000, 600, 48, 768, [10, 10], 6
+    cen = rs.standard_normal((40, d_search)).astype(np.float32) * 1.5
+
+    def draw(m):
+        x = rs.standard_normal((m, d_search)).astype(np.float32) + cen[rs.randint(0, 40, m)]
+        return (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float16)
+
+    X, Q = draw(n), draw(nq)
+    Xn, Qn = X[:, :d_nav].copy(), Q[:, :d_nav].copy()
+    root = seeded_layers(501, "MLP-6", d_nav, cats[0], scale=6.0)
+    internal = {(j, -1): seeded_layers(600 + j, "MLP-6", d_nav, cats[1], scale=6.0) for j in range(cats[0])}
+    pred = np.full((n, 2), -1, dtype=np.int64)
+    pred[:, 0] = orc.predict(root, orc.to_f32_tensor(Xn))
+    for (j, _), layers in internal.items():
+        rows = np.flatnonzero(pred[:, 0] == j)
+        if rows.size:
+            pred[rows, 1] = orc.predict(layers, orc.to_f32_tensor(Xn[rows]))
+    bucket_paths = sorted({tuple(int(v) for v in r) for r in pred})
+    li = LearnedIndex(root, internal, bucket_paths)
+    d, i, _ = li.search(None, Qn, X, Q, pred, cats, n_buckets=B, k=10)
+    idx = orc.OracleIndex(root, internal, bucket_paths)
+    exp_d, exp_i, _, exp_order = orc.search(idx, Qn, X, Q, pred, cats, n_buckets=B, k=10)
+    got_paths, _ = li._precompute_bucket_order(Qn, B, cats)
+    same = _multi_level_rows_equal(got_paths, exp_order, _oracle_node_probs(root, internal, Qn))
+    assert same.mean() > 0.99
+    assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what="multi-level medium")
+    with pytest.raises(ValueError):
+        li.search(None, Qn, X, Q, pred, cats, n_buckets=len(bucket_paths) + 1)

@@ -4,7 +4,8 @@ import numpy as np
 import pytest
 
 from oracle import lmi_oracle as orc
-from tests.golden_util import GoldenCase, case_names, assert_search_parity
+from tests.golden_util import (GoldenCase, MultiLevelCase, assert_search_parity, case_names,
+                               multi_level_case_names)
 
 
 @pytest.mark.parametrize("name", case_names())
@@ -41,3 +42,26 @@ def test_golden_covers_edge_cases():
     assert np.isinf(d).any(), "an empty bucket must have produced +inf fillers"
     assert ((d > 1e38) & ~np.isinf(d)).any(), "an undersized bucket must have produced FLT_MAX fillers"
     assert c.ids[0] == 1001
+
+
+@pytest.mark.parametrize("name", multi_level_case_names())
+def test_multi_level_search_matches_reference(name):
+    """n_levels > 1: best-first navigation (LearnedIndex.py:216-325) incl. a node without a
+    model, a populated path missing from bucket_paths and a model with fewer classes."""
+    c = MultiLevelCase(name)
+    index = orc.OracleIndex(c.root_layers, c.internal, c.bucket_paths)
+    for B, k in c.runs:
+        exp_order, exp_d, exp_i = c.expected(B, k)
+        d, i, _, order = orc.search(index, c.Q, c.X, c.Q, c.data_prediction, c.n_categories,
+                                    n_buckets=B, k=k, ids=c.ids)
+        assert order.dtype == np.int32 and order.shape == exp_order.shape == (c.Q.shape[0], B, len(c.n_categories))
+        assert np.array_equal(order, exp_order), f"{name} B={B}: bucket order differs"
+        assert_search_parity(d, i, exp_d, exp_i, rtol=1e-6, atol=1e-7, what=f"{name} B={B} k={k}")
+
+
+def test_multi_level_golden_covers_quirks():
+    c = MultiLevelCase("ml_3x3x2_quirks")
+    assert (2, 1, -1) not in c.internal and (0, 0, 1) not in c.bucket_paths
+    assert c.internal[(1, -1, -1)][-1][0].shape[0] == 2
+    assert (c.data_prediction == -1).any(), "rows under the model-less node keep an incomplete path"
+    assert ((c.data_prediction == np.array([0, 0, 1])).all(axis=1)).any(), "the unlisted path is populated"
