@@ -98,6 +98,7 @@ def test_plan_scan(nq, B, C, n, maxb):
 def test_flat_bucket_ids_follow_groupby_key_order():
     """Multi-level layout: flat id == rank of the path in groupby(category_L1..L) key order
     (LearnedIndex.py:343-350); incomplete paths go to one trailing, unprobeable bucket."""
+    import numpy as np
     from learnedmetricindex_b200.navigation import flat_bucket_ids, unflatten_bucket_ids
 
     cats = [3, 4, 2]
