@@ -246,7 +246,7 @@ def build_workload(args, device, rank, world, use_repo_kernels=True):
             xs = x if sel.numel() == m else x[sel].contiguous()
             if use_repo_kernels:
                 _native.check(L.lmi_scatter_rows(xs.data_ptr(), 1, dsel.data_ptr(), int(sel.numel()), D,
-                                                 vectors.data_ptr(), torch.cuda.current_stream().cuda_stream),
+                                                 vectors.data_ptr(), D, torch.cuda.current_stream().cuda_stream),
                               "lmi_scatter_rows")
                 torch.cuda.current_stream().synchronize()
             else:

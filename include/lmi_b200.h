@@ -118,9 +118,12 @@ int lmi_navigate_tree(const float *node_prob, int nq, int n_nodes, const int32_t
 
 /* ---- bucket layout ------------------------------------------------------------ */
 
-/* dst[dest_row[i], :] = (fp16) src[i, :] for i < m; src is fp32 or fp16 [m,d]. */
+/* dst[dest_row[i], 0:d] = (fp16) src[i, :] for i < m, and dst[dest_row[i], d:dst_ld] = 0; src is
+ * fp32 or fp16 [m,d], dst has a row pitch of dst_ld >= d elements (the scan kernel wants a
+ * multiple of 64: zero columns leave every inner product unchanged).  dest_row == NULL is the
+ * identity (cast + pad of a query matrix). */
 int lmi_scatter_rows(const void *src, int src_is_f16, const int64_t *dest_row, int64_t m, int d,
-                     void *dst_f16, void *stream);
+                     void *dst_f16, int dst_ld, void *stream);
 
 /* dst[i] = (fp16) src[i], count elements. */
 int lmi_cast_f16(const float *src, void *dst_f16, int64_t count, void *stream);

@@ -169,7 +169,7 @@ class LearnedIndex:
         C = layout.n_buckets
         k_out = PER_BUCKET_K if B == 1 else int(k)
         assert 0 < k_out <= PER_BUCKET_K * B, "k exceeds what n_buckets per-bucket top-10 lists can supply"
-        assert qs.shape[1] == layout.d, "query / data dimensionality mismatch"  # faiss: d == d2
+        assert qs.shape[1] == layout.d_data, "query / data dimensionality mismatch"  # faiss: d == d2
 
         def mark(i):
             if events is not None:
@@ -196,7 +196,11 @@ class LearnedIndex:
                 mark(i)
             return dists, nns
 
-        if qs.dtype == torch.float16:
+        if layout.d != layout.d_data:  # zero-pad K to the scan kernel's multiple of 64
+            q16 = torch.empty((nq, layout.d), dtype=torch.float16, device=dev)
+            _native.check(L.lmi_scatter_rows(qs.data_ptr(), int(qs.dtype == torch.float16), None, nq, layout.d_data,
+                                             q16.data_ptr(), layout.d, _stream_ptr()), "lmi_scatter_rows")
+        elif qs.dtype == torch.float16:
             q16 = qs
         else:
             q16 = torch.empty(qs.shape, dtype=torch.float16, device=dev)

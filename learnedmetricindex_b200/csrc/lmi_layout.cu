@@ -13,17 +13,18 @@ namespace lmi {
 // one warp per source row; 8-byte (4 x fp16) stores
 template <typename T>
 __global__ void scatter_rows_kernel(const T* __restrict__ src, const int64_t* __restrict__ dest_row, int64_t m, int d,
-                                    __half* __restrict__ dst) {
+                                    __half* __restrict__ dst, int ld) {
     const int warps = blockDim.x >> 5;
     const int lane = threadIdx.x & 31;
     for (int64_t i = (int64_t)blockIdx.x * warps + (threadIdx.x >> 5); i < m; i += (int64_t)gridDim.x * warps) {
-        const int64_t to = dest_row[i];
+        const int64_t to = dest_row ? dest_row[i] : i;
         const T* s = src + (size_t)i * d;
-        __half* o = dst + (size_t)to * d;
+        __half* o = dst + (size_t)to * ld;
         for (int c = lane; c < d; c += 32) {
             if constexpr (sizeof(T) == 2) o[c] = s[c];
             else o[c] = __float2half_rn(static_cast<float>(s[c]));
         }
+        for (int c = d + lane; c < ld; c += 32) o[c] = __float2half_rn(0.f);  // zero padding: inner products unchanged
     }
 }
 
@@ -36,8 +37,8 @@ __global__ void cast_f16_kernel(const float* __restrict__ src, __half* __restric
 }  // namespace lmi
 
 extern "C" int lmi_scatter_rows(const void* src, int src_is_f16, const int64_t* dest_row, int64_t m, int d,
-                                void* dst_f16, void* stream) {
-    if (!src || !dest_row || !dst_f16 || m < 0 || d <= 0) return LMI_E_BADARG;
+                                void* dst_f16, int dst_ld, void* stream) {
+    if (!src || !dst_f16 || m < 0 || d <= 0 || dst_ld < d) return LMI_E_BADARG;
     if (m == 0) return 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int warps = 8;
@@ -46,11 +47,11 @@ extern "C" int lmi_scatter_rows(const void* src, int src_is_f16, const int64_t* 
     if (src_is_f16)
         lmi::scatter_rows_kernel<__half><<<(unsigned)grid, warps * 32, 0, st>>>(static_cast<const __half*>(src),
                                                                                dest_row, m, d,
-                                                                               static_cast<__half*>(dst_f16));
+                                                                               static_cast<__half*>(dst_f16), dst_ld);
     else
         lmi::scatter_rows_kernel<float><<<(unsigned)grid, warps * 32, 0, st>>>(static_cast<const float*>(src),
                                                                               dest_row, m, d,
-                                                                              static_cast<__half*>(dst_f16));
+                                                                              static_cast<__half*>(dst_f16), dst_ld);
     return static_cast<int>(cudaGetLastError());
 }
 

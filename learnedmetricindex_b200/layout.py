@@ -27,15 +27,24 @@ def _stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+SCAN_K_MULTIPLE = 64  # lmi_scan_topk streams K in 128-byte (64 x fp16) swizzled boxes
+
+
+def padded_dim(d: int) -> int:
+    return -(-int(d) // SCAN_K_MULTIPLE) * SCAN_K_MULTIPLE
+
+
 class DeviceBucketLayout:
-    def __init__(self, vectors: torch.Tensor, bucket_off: torch.Tensor, ids: torch.Tensor, bucket_paths=None):
+    def __init__(self, vectors: torch.Tensor, bucket_off: torch.Tensor, ids: torch.Tensor, bucket_paths=None,
+                 d_data: Optional[int] = None):
         assert vectors.is_cuda and vectors.dtype == torch.float16 and vectors.is_contiguous()
         assert bucket_off.dtype == torch.int64 and ids.dtype == torch.int32
         self.vectors = vectors
         self.bucket_off = bucket_off.to(vectors.device)
         self.bucket_off_host = bucket_off.cpu().numpy()
         self.ids = ids
-        self.n, self.d = vectors.shape
+        self.n, self.d = vectors.shape  # d: row pitch (padded to a multiple of 64 with zero columns)
+        self.d_data = int(d_data) if d_data is not None else self.d  # the data's own dimensionality
         self.n_buckets = self.bucket_off_host.shape[0] - 1
         sizes = np.diff(self.bucket_off_host)
         self.max_bucket = int(sizes.max()) if sizes.size else 0
@@ -68,7 +77,8 @@ class DeviceBucketLayout:
         ids32 = (ids_sorted & 0xFFFFFFFF).to(torch.int64)
         ids32 = torch.where(ids32 >= 2 ** 31, ids32 - 2 ** 32, ids32).to(torch.int32).contiguous()
         del order
-        out = torch.empty((max(n_kept, 1), d), dtype=torch.float16, device=dev)
+        ld = padded_dim(d)
+        out = torch.empty((max(n_kept, 1), ld), dtype=torch.float16, device=dev)
         if n_kept < n:
             # dropped rows scatter past the end: give them a scratch destination inside bounds
             raise NotImplementedError("rows without a bucket are not supported")
@@ -76,10 +86,10 @@ class DeviceBucketLayout:
         for s in range(0, n, chunk):
             m = min(chunk, n - s)
             _native.check(L.lmi_scatter_rows(x[s : s + m].data_ptr(), int(x.dtype == torch.float16),
-                                             dest[s : s + m].data_ptr(), m, d, out.data_ptr(), _stream_ptr()),
+                                             dest[s : s + m].data_ptr(), m, d, out.data_ptr(), ld, _stream_ptr()),
                           "lmi_scatter_rows")
         torch.cuda.current_stream().synchronize()
-        return cls(out[:n_kept] if n_kept else out[:0], off, ids32, bucket_paths)
+        return cls(out[:n_kept] if n_kept else out[:0], off, ids32, bucket_paths, d_data=d)
 
     @classmethod
     def from_host(cls, data_search, labels: np.ndarray, n_buckets: int, ids: Optional[np.ndarray] = None,
@@ -110,7 +120,8 @@ class DeviceBucketLayout:
         dest = np.empty(n, dtype=np.int64)
         dest[order] = np.arange(n, dtype=np.int64)
         ids32 = torch.from_numpy((ids[order] & 0xFFFFFFFF).astype(np.uint32).view(np.int32).copy()).to(dev)
-        out = torch.empty((max(n, 1), d), dtype=torch.float16, device=dev)
+        ld = padded_dim(d)
+        out = torch.empty((max(n, 1), ld), dtype=torch.float16, device=dev)
         is_f16 = mat.dtype == np.float16
         if mat.dtype not in (np.float16, np.float32):
             mat = mat.astype(np.float32)
@@ -119,9 +130,9 @@ class DeviceBucketLayout:
             blk = torch.from_numpy(np.ascontiguousarray(mat[s : s + m])).to(dev)
             dst = torch.from_numpy(dest[s : s + m]).to(dev)
             _native.check(L.lmi_scatter_rows(blk.data_ptr(), int(is_f16), dst.data_ptr(), m, d, out.data_ptr(),
-                                             _stream_ptr()), "lmi_scatter_rows")
+                                             ld, _stream_ptr()), "lmi_scatter_rows")
             torch.cuda.current_stream().synchronize()
-        return cls(out[:n], torch.from_numpy(off), ids32, bucket_paths)
+        return cls(out[:n], torch.from_numpy(off), ids32, bucket_paths, d_data=d)
 
     # ------------------------------------------------------------------------------
     def restrict_to_buckets(self, mine: Sequence[int]) -> "DeviceBucketLayout":
@@ -138,4 +149,5 @@ class DeviceBucketLayout:
         vec = self.vectors[sel].contiguous() if sel.numel() else self.vectors[:0]
         if vec.shape[0] == 0:
             vec = torch.zeros((1, self.d), dtype=torch.float16, device=self.device)[:0]
-        return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths)
+        return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths,
+                                  d_data=self.d_data)

@@ -347,3 +347,26 @@ def test_multi_level_medium_matches_oracle():
     assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what="multi-level medium")
     with pytest.raises(ValueError):
         li.search(None, Qn, X, Q, pred, cats, n_buckets=len(bucket_paths) + 1)
+
+
+@pytest.mark.parametrize("d", [96, 100, 30])
+def test_dimensions_that_are_not_multiples_of_64(d):
+    """pca32 / pca96 style representations (search/search.py:192-216): the layout pads K with zero
+    columns to the scan kernel's multiple of 64; results are those of the unpadded data."""
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(d)
+    n, nq, C, B = 6000, 300, 7, 3
+    X = rs.standard_normal((n, d)).astype(np.float32)
+    X = (X / np.linalg.norm(X, axis=1, keepdims=True)).astype(np.float16)
+    Q = rs.standard_normal((nq, d)).astype(np.float32)
+    Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+    layers = seeded_layers(900 + d, "MLP-6", d, C, scale=4.0)
+    pred = orc.predict(layers, orc.to_f32_tensor(X)).astype(np.int64).reshape(-1, 1)
+    li = _index(layers, C)
+    dd, ii, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=B, k=10)
+    exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=10)
+    probs, _ = orc.predict_proba(layers, orc.to_f32_tensor(Q))
+    same = _order_rows_equal(li.last_bucket_order.cpu().numpy(), exp_order[:, :, 0], probs)
+    assert same.mean() > 0.99
+    assert_search_parity(dd[same], ii[same], exp_d[same], exp_i[same], what=f"d={d}")
