@@ -85,6 +85,18 @@ int lmi_linear_tc(const float *x_hi, const float *x_mid, const float *x_lo,
                   int nq, int in_dim, int out_dim, int relu,
                   float *y, float *y_hi, float *y_mid, float *y_lo, void *stream);
 
+/* Grouped form -- every internal model of one tree level in ONE launch (blockIdx.z = model g):
+ *   x parts  [nq, ldx]: model g reads columns [g*in_dim, (g+1)*in_dim)  (the previous grouped layer's
+ *                       output; for a first layer stack the W of all models and call lmi_linear_tc)
+ *   w parts  [groups, out_dim, in_dim] contiguous, bias [groups, out_dim]
+ *   y / y parts: row pitch ldy, model g writes columns [y_col0 + g*out_dim, y_col0 + (g+1)*out_dim)
+ * so the last layer can write its logits straight into the node table of lmi_navigate_tree. */
+int lmi_linear_tc_grouped(const float *x_hi, const float *x_mid, const float *x_lo, int ldx,
+                          const float *w_hi, const float *w_mid, const float *w_lo, const float *bias,
+                          int nq, int in_dim, int out_dim, int groups, int relu,
+                          float *y, float *y_hi, float *y_mid, float *y_lo, int ldy, int y_col0,
+                          void *stream);
+
 /* softmax over the C logits of each row, then the B most probable classes in
  * descending probability (ties: lower class index first).
  * bucket_order int32[nq,B] (== the reference's bucket_order[:, :, 0]), probs f32[nq,B]. */
@@ -103,6 +115,12 @@ int lmi_argmax(const float *logits, int64_t n, int C, int64_t *out, void *stream
 /* probs[q*out_stride + out_col0 + c] = softmax(logits[q, :])[c]  (model.py:238), C columns. */
 int lmi_softmax_probs(const float *logits, int nq, int C, float *probs, int64_t out_stride,
                       int64_t out_col0, void *stream);
+
+/* In-place softmax of n_seg column segments of table[nq, ld]: segment s covers columns
+ * [seg_start[s], seg_start[s] + seg_len[s]); seg_len[s] <= 0 is skipped.  One segment per
+ * model: the root's [0, C1) and, for every node with a model, its children's columns. */
+int lmi_softmax_segments(float *table, int nq, int64_t ld, const int32_t *seg_start,
+                         const int32_t *seg_len, int n_seg, void *stream);
 
 /* Per query: best-first search over the tree.  The frontier starts as the n_roots depth-1
  * nodes; the most probable frontier node is popped (ties: lowest node id; the reference's

@@ -60,6 +60,10 @@ _SIGNATURES = {
     "lmi_split_tf32": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lmi_linear_tc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                               c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "lmi_linear_tc_grouped": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_int, c_int, c_void_p]),
+    "lmi_softmax_segments": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
     "lmi_softmax_topn": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "lmi_argmax": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "lmi_softmax_probs": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p]),

@@ -79,7 +79,7 @@ struct TcBarriers {
 __global__ void __launch_bounds__(TC_THREADS)
 linear_tc_kernel(const __grid_constant__ TcMaps maps, int na, int nb, uint32_t terms, int nterms, int stages,
                  const float* __restrict__ bias, int M, int K, int N, int relu, float* __restrict__ y,
-                 float* __restrict__ y_hi, float* __restrict__ y_mid, float* __restrict__ y_lo) {
+                 float* __restrict__ y_hi, float* __restrict__ y_mid, float* __restrict__ y_lo, int ldy, int ycol0) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int stage_bytes = na * TC_A_BYTES + nb * TC_B_BYTES;
@@ -87,6 +87,7 @@ linear_tc_kernel(const __grid_constant__ TcMaps maps, int na, int nb, uint32_t t
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * TC_BN, m0 = blockIdx.y * TC_BM;
+    const int grp = blockIdx.z;  // grouped form: model `grp` of a tree level (x columns, W rows, y columns of its own)
     const int KB = (K + TC_BK - 1) / TC_BK;
 
     if (warp == 4 && lane == 0) {
@@ -122,9 +123,9 @@ linear_tc_kernel(const __grid_constant__ TcMaps maps, int na, int nb, uint32_t t
                 uint8_t* dst = ring + (size_t)stage * stage_bytes;
                 ptx::mbar_arrive_expect_tx(&bars->full[stage], stage_bytes);
                 for (int i = 0; i < na; ++i)
-                    ptx::tma_load_2d(dst + i * TC_A_BYTES, &maps.a[i], kb * TC_BK, m0, &bars->full[stage], pol_x);
+                    ptx::tma_load_3d(dst + i * TC_A_BYTES, &maps.a[i], kb * TC_BK, m0, grp, &bars->full[stage], pol_x);
                 for (int i = 0; i < nb; ++i)
-                    ptx::tma_load_2d(dst + na * TC_A_BYTES + i * TC_B_BYTES, &maps.b[i], kb * TC_BK, n0,
+                    ptx::tma_load_3d(dst + na * TC_A_BYTES + i * TC_B_BYTES, &maps.b[i], kb * TC_BK, n0, grp,
                                      &bars->full[stage], pol_w);
             }
             __syncwarp();
@@ -193,18 +194,20 @@ linear_tc_kernel(const __grid_constant__ TcMaps maps, int na, int nb, uint32_t t
         }
         const int r = m0 + warp * 32 + lane;
         if (r < M) {
-            const bool vec = (N % 4 == 0);
+            const int gcol0 = ycol0 + grp * N;  // first output column of this group
+            const float* gbias = bias + (size_t)grp * N;
+            const bool vec = (N % 4 == 0) && (ldy % 4 == 0) && (gcol0 % 4 == 0);
 #pragma unroll
             for (int j = 0; j < TC_BN; j += 4) {
                 float o[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const int c = n0 + j + u;
-                    float t = acc[j + u] + (c < N ? bias[c] : 0.f);
+                    float t = acc[j + u] + (c < N ? gbias[c] : 0.f);
                     if (relu) t = fmaxf(t, 0.f);
                     o[u] = t;
                 }
-                const size_t off = (size_t)r * N + n0 + j;
+                const size_t off = (size_t)r * ldy + gcol0 + n0 + j;
                 if (vec && n0 + j + 3 < N) {
                     if (y) *reinterpret_cast<float4*>(y + off) = make_float4(o[0], o[1], o[2], o[3]);
                     if (y_hi) {
@@ -256,15 +259,18 @@ static TcEncodeTiledFn tc_encode_fn() {
     return fn;
 }
 
-// fp32 matrix [rows, K] row-major -> boxes of 32 fp32 x box_rows rows, SWIZZLE_128B, zero fill out of bounds
-static bool tc_make_map(CUtensorMap* map, const float* base, int64_t rows, int K, int box_rows) {
+// `groups` fp32 matrices [rows, K] -- matrix g starts `group_stride` elements after matrix g-1, rows are `ld`
+// elements apart -> boxes of 32 fp32 x box_rows rows x 1 group, SWIZZLE_128B, zero fill out of bounds
+static bool tc_make_map(CUtensorMap* map, const float* base, int64_t rows, int K, int box_rows, int64_t ld,
+                        int groups, int64_t group_stride) {
     TcEncodeTiledFn encode = tc_encode_fn();
     if (!encode) return false;
-    const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-    const cuuint64_t gstride[1] = {(cuuint64_t)K * sizeof(float)};
-    const cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
-    const cuuint32_t estride[2] = {1, 1};
-    return encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estride,
+    const cuuint64_t gdim[3] = {(cuuint64_t)K, (cuuint64_t)rows, (cuuint64_t)groups};
+    const cuuint64_t gstride[2] = {(cuuint64_t)ld * sizeof(float),
+                                   (cuuint64_t)(groups > 1 ? group_stride : ld * rows) * sizeof(float)};
+    const cuuint32_t box[3] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows, 1};
+    const cuuint32_t estride[3] = {1, 1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), gdim, gstride, box, estride,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
@@ -288,7 +294,18 @@ extern "C" int lmi_split_tf32(const void* x, int x_is_f16, int64_t count, float*
 extern "C" int lmi_linear_tc(const float* x_hi, const float* x_mid, const float* x_lo, const float* w_hi,
                              const float* w_mid, const float* w_lo, const float* bias, int nq, int in_dim,
                              int out_dim, int relu, float* y, float* y_hi, float* y_mid, float* y_lo, void* stream) {
+    return lmi_linear_tc_grouped(x_hi, x_mid, x_lo, in_dim, w_hi, w_mid, w_lo, bias, nq, in_dim, out_dim, 1, relu, y,
+                                 y_hi, y_mid, y_lo, out_dim, 0, stream);
+}
+
+extern "C" int lmi_linear_tc_grouped(const float* x_hi, const float* x_mid, const float* x_lo, int ldx,
+                                     const float* w_hi, const float* w_mid, const float* w_lo, const float* bias,
+                                     int nq, int in_dim, int out_dim, int groups, int relu, float* y, float* y_hi,
+                                     float* y_mid, float* y_lo, int ldy, int y_col0, void* stream) {
     if (!x_hi || !w_hi || !bias || nq < 0 || in_dim <= 0 || out_dim <= 0) return LMI_E_BADARG;
+    if (groups <= 0 || groups > 65535 || ldx < groups * in_dim || y_col0 < 0 || ldy < y_col0 + groups * out_dim)
+        return LMI_E_BADARG;
+    if (ldx % 4 != 0) return LMI_E_UNSUPPORTED;
     if ((x_mid == nullptr) != (x_lo == nullptr) || (w_mid == nullptr) != (w_lo == nullptr)) return LMI_E_BADARG;
     if (!y && !y_hi) return LMI_E_BADARG;
     if (y_hi && (!y_mid || !y_lo)) return LMI_E_BADARG;
@@ -305,9 +322,11 @@ extern "C" int lmi_linear_tc(const float* x_hi, const float* x_mid, const float*
 
     lmi::TcMaps maps;
     for (int i = 0; i < na; ++i)
-        if (!lmi::tc_make_map(&maps.a[i], xa[i], nq, in_dim, lmi::TC_BM)) return LMI_E_DRIVER;
+        if (!lmi::tc_make_map(&maps.a[i], xa[i], nq, in_dim, lmi::TC_BM, ldx, groups, in_dim)) return LMI_E_DRIVER;
     for (int i = 0; i < nb; ++i)
-        if (!lmi::tc_make_map(&maps.b[i], wb[i], out_dim, in_dim, lmi::TC_BN)) return LMI_E_DRIVER;
+        if (!lmi::tc_make_map(&maps.b[i], wb[i], out_dim, in_dim, lmi::TC_BN, in_dim, groups,
+                              (int64_t)out_dim * in_dim))
+            return LMI_E_DRIVER;
     for (int i = na; i < 3; ++i) maps.a[i] = maps.a[0];
     for (int i = nb; i < 3; ++i) maps.b[i] = maps.b[0];
 
@@ -328,8 +347,8 @@ extern "C" int lmi_linear_tc(const float* x_hi, const float* x_mid, const float*
     const size_t smem = (size_t)stages * stage_bytes + 1024 + sizeof(lmi::TcBarriers);
     cudaError_t e = cudaFuncSetAttribute(lmi::linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    dim3 grid((out_dim + lmi::TC_BN - 1) / lmi::TC_BN, (nq + lmi::TC_BM - 1) / lmi::TC_BM);
+    dim3 grid((out_dim + lmi::TC_BN - 1) / lmi::TC_BN, (nq + lmi::TC_BM - 1) / lmi::TC_BM, groups);
     lmi::linear_tc_kernel<<<grid, lmi::TC_THREADS, smem, st>>>(maps, na, nb, terms, nterms, stages, bias, nq, in_dim,
-                                                               out_dim, relu, y, y_hi, y_mid, y_lo);
+                                                               out_dim, relu, y, y_hi, y_mid, y_lo, ldy, y_col0);
     return static_cast<int>(cudaGetLastError());
 }

@@ -51,6 +51,27 @@ __global__ void softmax_probs_kernel(const float* __restrict__ logits, int nq, i
     for (int c = lane; c < C; c += 32) dst[c] = expf(src[c] - mx) / sum;
 }
 
+// In-place softmax of column segments (one per model) of the node table; one warp per (query, segment).
+__global__ void softmax_segments_kernel(float* __restrict__ table, int nq, int64_t ld,
+                                        const int32_t* __restrict__ seg_start, const int32_t* __restrict__ seg_len,
+                                        int n_seg) {
+    const int warps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * warps + warp;
+    if (w >= (int64_t)nq * n_seg) return;
+    const int q = (int)(w / n_seg), s = (int)(w % n_seg);
+    const int C = seg_len[s];
+    if (C <= 0) return;
+    float* row = table + (size_t)q * ld + seg_start[s];
+    float mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, row[c]);
+    mx = nav_warp_max(mx);
+    float sum = 0.f;
+    for (int c = lane; c < C; c += 32) sum += expf(row[c] - mx);
+    sum = nav_warp_sum(sum);
+    for (int c = lane; c < C; c += 32) row[c] = expf(row[c] - mx) / sum;
+}
+
 // One warp per query.  smem: frontier[warps][n_nodes].
 __global__ void navigate_tree_kernel(const float* __restrict__ node_prob, int nq, int n_nodes,
                                      const int32_t* __restrict__ first_child, const int32_t* __restrict__ n_children,
@@ -114,6 +135,18 @@ extern "C" int lmi_softmax_probs(const float* logits, int nq, int C, float* prob
     const int warps = 8;
     lmi::softmax_probs_kernel<<<(nq + warps - 1) / warps, warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
         logits, nq, C, probs, out_stride, out_col0);
+    return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lmi_softmax_segments(float* table, int nq, int64_t ld, const int32_t* seg_start,
+                                    const int32_t* seg_len, int n_seg, void* stream) {
+    if (!table || !seg_start || !seg_len || nq < 0 || ld <= 0 || n_seg <= 0) return LMI_E_BADARG;
+    if (nq == 0) return 0;
+    const int warps = 8;
+    const int64_t blocks = ((int64_t)nq * n_seg + warps - 1) / warps;
+    if (blocks > 0x7fffffff) return LMI_E_UNSUPPORTED;
+    lmi::softmax_segments_kernel<<<(unsigned)blocks, warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        table, nq, ld, seg_start, seg_len, n_seg);
     return static_cast<int>(cudaGetLastError());
 }
 

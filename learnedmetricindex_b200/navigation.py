@@ -20,6 +20,7 @@ Flat bucket id of a full path ``(c_0, ..., c_{L-1})`` = mixed radix over ``n_cat
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Sequence, Tuple
 
 import numpy as np
@@ -68,6 +69,7 @@ class NavigationTree:
         assert L >= 2
         self.device = root_model.device
         self.root_model = root_model
+        self.grouped = os.environ.get("LMI_NAV_GROUPED", "1") != "0"  # 0: one launch set per model (verification)
         # :222 seeds the queue with pred_l1_paths[:, :n_categories[0]]
         assert root_model.n_output_neurons == self.n_categories[0], \
             "root model outputs != n_categories[0]"
@@ -81,6 +83,7 @@ class NavigationTree:
         node_bucket = np.full(self.n_nodes, -1, dtype=np.int32)
 
         self.models: List[Tuple[int, NeuralNetwork]] = []  # (first child column, model)
+        by_depth: Dict[int, Dict[int, NeuralNetwork]] = {}  # depth -> {flat prefix: model}
         for path, model in internal_models.items():
             path = tuple(int(v) for v in path)
             depth = len(path) - path.count(EMPTY_VALUE)  # :283
@@ -96,6 +99,7 @@ class NavigationTree:
             first_child[v] = fc
             n_children[v] = model.n_output_neurons
             self.models.append((fc, model))
+            by_depth.setdefault(depth, {})[self._flat(path[:depth])] = model
         for path in bucket_paths:
             path = tuple(int(v) for v in path)
             assert len(path) == L, f"bucket path {path} does not have {L} levels"
@@ -107,6 +111,12 @@ class NavigationTree:
         self.n_children = torch.from_numpy(n_children).to(self.device)
         self.node_bucket = torch.from_numpy(node_bucket).to(self.device)
         self.n_reachable_buckets = self._count_reachable()
+        # one softmax segment per model: the root's [0, C1) and every internal model's child columns
+        seg_start = [0] + [fc for fc, _ in self.models]
+        seg_len = [self.n_roots] + [m.n_output_neurons for _, m in self.models]
+        self.seg_start = torch.tensor(seg_start, dtype=torch.int32, device=self.device)
+        self.seg_len = torch.tensor(seg_len, dtype=torch.int32, device=self.device)
+        self._groups = self._stack_levels(by_depth)
 
     def _flat(self, prefix: Sequence[int]) -> int:
         f = 0
@@ -128,6 +138,87 @@ class NavigationTree:
             stack.extend(range(fc, fc + nc))
         return found
 
+    # ------------------------------------------------------------------ grouped inference
+    def _stack_levels(self, by_depth):
+        """Per depth: the models of ALL nodes of that depth stacked for the grouped tensor-core
+        launches (``lmi_linear_tc`` on the stacked first layer, ``lmi_linear_tc_grouped`` after),
+        node order == column order of the table.  ``None`` when the level is not uniform enough
+        (different layer shapes) or the tensor-core path does not apply; the per-model loop of
+        ``node_probabilities`` covers that."""
+        if not self.root_model._tc_ok():
+            return None
+        levels = []
+        for depth in sorted(by_depth):
+            models = by_depth[depth]
+            G = int(np.prod(self.n_categories[:depth]))
+            shapes = {tuple(tuple(W.shape) for W, _ in m.layers[:-1]) + (m.layers[-1][0].shape[1],)
+                      for m in models.values()}
+            if len(shapes) != 1 or not all(m._tc_ok() for m in models.values()):
+                return None
+            proto = next(iter(models.values()))
+            n_layers = len(proto.layers)
+            c_pad = self.n_categories[depth]
+            stacked = []
+            for i in range(n_layers):
+                out_i = c_pad if i + 1 == n_layers else proto.layers[i][0].shape[0]
+                in_i = proto.layers[i][0].shape[1]
+                if in_i % 4:
+                    return None
+                W = torch.zeros((G, out_i, in_i), dtype=torch.float32, device=self.device)
+                b = torch.zeros((G, out_i), dtype=torch.float32, device=self.device)
+                for g, m in models.items():
+                    Wm, bm = m.layers[i]
+                    W[g, : Wm.shape[0]] = Wm
+                    b[g, : bm.shape[0]] = bm
+                stacked.append(dict(W=W.contiguous(), b=b.contiguous(), parts=None, in_dim=in_i, out_dim=out_i))
+            levels.append(dict(G=G, col0=int(self.base[depth]), layers=stacked))
+        return levels
+
+    def _forward_into_table(self, x_parts, d_in, G, layers, table, col0, split):
+        """Runs ``G`` stacked models (shared input ``x_parts``) and writes the last layer's logits
+        into ``table[:, col0 : col0 + G*out]``."""
+        L = _native.lib()
+        nq = table.shape[0]
+        ptr = lambda t: t.data_ptr() if t is not None else None
+        parts, ldx = x_parts, d_in
+        for i, lyr in enumerate(layers):
+            if lyr["parts"] is None:
+                lyr["parts"] = split(lyr["W"], False)
+            wp = lyr["parts"]
+            last = i + 1 == len(layers)
+            width = G * lyr["out_dim"]
+            if last:
+                y, nxt, ldy, ycol = table, (None, None, None), table.shape[1], col0
+            else:
+                y, ldy, ycol = None, width, 0
+                nxt = tuple(torch.empty((nq, width), dtype=torch.float32, device=self.device) for _ in range(3))
+            if i == 0:  # shared input: one plain launch over the stacked output features
+                groups, in_dim, out_dim = 1, d_in, width
+            else:
+                groups, in_dim, out_dim = G, lyr["in_dim"], lyr["out_dim"]
+            _native.check(L.lmi_linear_tc_grouped(ptr(parts[0]), ptr(parts[1]), ptr(parts[2]), ldx, ptr(wp[0]),
+                                                  ptr(wp[1]), ptr(wp[2]), lyr["b"].data_ptr(), nq, in_dim, out_dim,
+                                                  groups, int(not last), ptr(y), ptr(nxt[0]), ptr(nxt[1]),
+                                                  ptr(nxt[2]), ldy, ycol, _stream_ptr()), "lmi_linear_tc_grouped")
+            parts, ldx = nxt, width
+
+    def _node_probabilities_grouped(self, qn: torch.Tensor) -> torch.Tensor:
+        L = _native.lib()
+        nq = qn.shape[0]
+        table = torch.empty((nq, self.n_nodes), dtype=torch.float32, device=self.device)
+        root = self.root_model
+        parts = root.split_input(qn)
+        if getattr(self, "_root_stack", None) is None:
+            self._root_stack = [dict(W=W, b=b, parts=None, in_dim=W.shape[1], out_dim=W.shape[0])
+                                for W, b in root.layers]
+        self._forward_into_table(parts, root.input_dim, 1, self._root_stack, table, 0, root._split)
+        for lvl in self._groups:
+            self._forward_into_table(parts, root.input_dim, lvl["G"], lvl["layers"], table, lvl["col0"], root._split)
+        _native.check(L.lmi_softmax_segments(table.data_ptr(), nq, self.n_nodes, self.seg_start.data_ptr(),
+                                             self.seg_len.data_ptr(), int(self.seg_start.shape[0]), _stream_ptr()),
+                      "lmi_softmax_segments")
+        return table
+
     # ----------------------------------------------------------------------------------
     def node_probabilities(self, qn: torch.Tensor) -> torch.Tensor:
         """f32[nq, n_nodes]: root probabilities in columns [0, C1), every internal model's
@@ -137,6 +228,8 @@ class NavigationTree:
         table = torch.empty((nq, self.n_nodes), dtype=torch.float32, device=self.device)
         if nq == 0:
             return table
+        if self._groups is not None and self.grouped:
+            return self._node_probabilities_grouped(qn)
         parts = self.root_model.split_input(qn)  # one hi/mid/lo split shared by every model
         for col0, model in [(0, self.root_model)] + self.models:
             logits = model.logits(qn, parts=parts)

@@ -161,3 +161,31 @@ def build_standin_index(
 
 def layers_to_numpy(layers):
     return [(W.detach().cpu().numpy().astype(np.float32), b.detach().cpu().numpy().astype(np.float32)) for W, b in layers]
+
+
+def build_standin_index_two_level(
+    x_nav: torch.Tensor, n_categories, model_type: str = "MLP", train_rows: int = 200_000,
+    kmeans_iters: int = 8, steps: int = 200, lr: float = 0.01, seed: int = SEED,
+):
+    """2-level contract of ``LearnedIndexBuilder.build`` (LearnedIndexBuilder.py:67-107, :203-280):
+    root model over all rows, one internal model per level-1 class trained on the rows the root
+    routes there, ``data_prediction[:, 1]`` = that model's argmax, ``bucket_paths`` =
+    ``(j, 0..len(unique(predictions))-1)`` (:276-278).  A level-1 class without rows gets no model
+    (the reference's builder would assert, :243-245; search handles the missing model, :269-273).
+    Returns ``(root_layers, {path: layers}, data_prediction int64[n,2], bucket_paths)``."""
+    c1, c2 = (int(c) for c in n_categories)
+    root_layers, pred0 = build_standin_index(x_nav, c1, model_type, train_rows, kmeans_iters, steps, lr, seed)
+    n = x_nav.shape[0]
+    pred = torch.full((n, 2), -1, dtype=torch.int64, device=x_nav.device)
+    pred[:, 0] = pred0[:, 0]
+    internal, bucket_paths = {}, []
+    for j in range(c1):
+        rows = torch.nonzero(pred[:, 0] == j).reshape(-1)
+        if rows.numel() < 2 * c2:
+            continue
+        layers, p = build_standin_index(x_nav[rows], c2, model_type, train_rows, kmeans_iters, steps, lr,
+                                        seed + 1 + j)
+        internal[(j, -1)] = layers
+        pred[rows, 1] = p[:, 0]
+        bucket_paths += [(j, b) for b in range(int(torch.unique(p[:, 0]).numel()))]
+    return root_layers, internal, pred, bucket_paths

@@ -370,3 +370,47 @@ def test_dimensions_that_are_not_multiples_of_64(d):
     same = _order_rows_equal(li.last_bucket_order.cpu().numpy(), exp_order[:, :, 0], probs)
     assert same.mean() > 0.99
     assert_search_parity(dd[same], ii[same], exp_d[same], exp_i[same], what=f"d={d}")
+
+
+def test_grouped_navigation_inference_equals_per_model_loop():
+    """lmi_linear_tc_grouped (all models of a level in one launch, logits written straight into the
+    node table) against the per-model launches: same split-precision arithmetic, so the
+    probabilities of every reachable node must agree to the last bit -- incl. a 2-hidden-layer
+    model type (grouped middle layer), a missing model and a model with fewer classes."""
+    from learnedmetricindex_b200 import LearnedIndex
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(77)
+    for cats, inner, d in [([5, 4], "MLP", 96), ([3, 3, 2], "MLP-5", 64), ([4, 6], "MLP-7", 768)]:
+        L = len(cats)
+        Q = rs.standard_normal((777, d)).astype(np.float32)
+        Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+        root = seeded_layers(1, "MLP-6", d, cats[0], scale=4.0)
+        internal = {}
+        import itertools
+        for depth in range(1, L):
+            for j, prefix in enumerate(itertools.product(*[range(c) for c in cats[:depth]])):
+                if depth == 1 and j == 1:
+                    continue  # node without a model
+                n_out = cats[depth] - 1 if (depth == 1 and j == 0) else cats[depth]
+                internal[tuple(prefix) + (-1,) * (L - depth)] = seeded_layers(50 + 7 * depth + j, inner, d, n_out, 4.0)
+        bucket_paths = list(itertools.product(*[range(c) for c in cats]))
+        li = LearnedIndex(root, internal, bucket_paths)
+        tree = li.navigation_tree(cats)
+        assert tree._groups is not None
+        qd = torch.from_numpy(Q).cuda()
+        tree.grouped = True
+        t_grouped = tree.node_probabilities(qd).cpu().numpy()
+        tree.grouped = False
+        t_loop = tree.node_probabilities(qd).cpu().numpy()
+        cols = np.zeros(tree.n_nodes, dtype=bool)
+        for s0, ln in zip(tree.seg_start.cpu().numpy(), tree.seg_len.cpu().numpy()):
+            cols[s0 : s0 + ln] = True
+        assert cols.sum() > cats[0]
+        np.testing.assert_array_equal(t_grouped[:, cols], t_loop[:, cols])
+        B = min(5, tree.n_reachable_buckets)
+        tree.grouped = True
+        o1, _ = tree.bucket_order(qd, B)
+        tree.grouped = False
+        o2, _ = tree.bucket_order(qd, B)
+        assert torch.equal(o1, o2)
