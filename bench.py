@@ -545,8 +545,9 @@ def main():
     scan_s = float(np.mean(scan_ms)) / 1e3
     t_tensor, t_hbm = flops / (tf_peak * 1e12), bytes_alg / (hbm_peak * 1e9)
     traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get(args.workload)
+    try:  # ncu dram bytes of one launch: only valid for the exact single-GPU default configuration it was taken on
+        if world == 1 and not (args.n or args.nq or args.buckets) and args.probe == 4:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get(args.workload)
     except Exception:
         pass
     if t_tensor >= t_hbm:
