@@ -414,3 +414,38 @@ def test_grouped_navigation_inference_equals_per_model_loop():
         tree.grouped = False
         o2, _ = tree.bucket_order(qd, B)
         assert torch.equal(o1, o2)
+
+
+def test_property_ragged_buckets_match_oracle():
+    """Hypothesis over ragged bucket sizes (incl. s_b < 10 and empty buckets), query counts that
+    leave partial tiles, B = 1 .. C, k <= 10 and odd dimensionalities."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+    from tests.golden_util import seeded_layers
+
+    @settings(max_examples=30, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+    @given(st.integers(0, 10_000), st.integers(1, 9), st.integers(1, 260), st.sampled_from([8, 24, 64, 100, 192]),
+           st.integers(1, 10), st.data())
+    def run(seed, C, nq, d, k, data):
+        rs = np.random.RandomState(seed)
+        B = data.draw(st.integers(1, C))
+        sizes = rs.choice([0, 1, 3, 9, 10, 11, 64, 65, 300, 1500], size=C)
+        if sizes.sum() == 0:
+            sizes[0] = 5
+        n = int(sizes.sum())
+        pred = rs.permutation(np.repeat(np.arange(C), sizes)).astype(np.int64).reshape(-1, 1)
+        X = rs.standard_normal((n, d)).astype(np.float32)
+        X = (X / np.linalg.norm(X, axis=1, keepdims=True)).astype(np.float16)
+        Q = rs.standard_normal((nq, d)).astype(np.float32)
+        Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+        layers = seeded_layers(seed + 5, "MLP-8", d, C, scale=4.0)
+        ids = rs.permutation(np.arange(7, 7 + n))
+        li = _index(layers, C)
+        li.attach_layout(__import__("learnedmetricindex_b200").DeviceBucketLayout.from_host(X, pred[:, 0], C, ids=ids))
+        dd, ii, _ = li.search(None, Q, None, Q, None, [C], n_buckets=B, k=k)
+        exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=k, ids=ids)
+        probs, _ = orc.predict_proba(layers, orc.to_f32_tensor(Q))
+        same = _order_rows_equal(li.last_bucket_order.cpu().numpy(), exp_order[:, :, 0], probs)
+        assert_search_parity(dd[same], ii[same], exp_d[same], exp_i[same],
+                             what=f"seed={seed} C={C} nq={nq} d={d} B={B} k={k} sizes={sizes.tolist()}")
+
+    run()
