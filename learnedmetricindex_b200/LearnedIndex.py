@@ -35,6 +35,8 @@ MAX_RANGES = 32  # row ranges a bucket is cut into at most
 LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
 DEFAULT_RANGE_ROWS = 16384  # upper bound on the rows of a scan work item (see plan_scan)
+GRAPH_MAX_NQ = int(os.environ.get("LMI_GRAPH_MAX_NQ", 4096))  # `search` replays a CUDA graph up to this batch size
+GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index
 
 
 def _stream_ptr() -> int:
@@ -76,6 +78,7 @@ class LearnedIndex:
         self.bucket_paths = [tuple(p) for p in (bucket_paths or [])]
         """List of paths to the buckets."""
         self.scan_impl = scan_impl  # 0: tcgen05/TMA kernel; 1: CUDA-core verification kernel (tests)
+        self.use_graphs = os.environ.get("LMI_CUDA_GRAPH", "1") != "0"
         self.device = self.root_model.device
         self._layout: Optional[DeviceBucketLayout] = None
         self._layout_key = None
@@ -83,6 +86,7 @@ class LearnedIndex:
         self.last_bucket_order: Optional[torch.Tensor] = None
         self.last_probs: Optional[torch.Tensor] = None
         self._tree: Optional[NavigationTree] = None
+        self._graphs: Dict[tuple, dict] = {}
         self._n_sms = torch.cuda.get_device_properties(self.device).multi_processor_count
 
     @classmethod
@@ -96,6 +100,7 @@ class LearnedIndex:
         self._layout = layout
         self._layout_key = "attached"
         self._layout_refs = None
+        self._graphs.clear()  # captured graphs hold pointers into the previous layout
 
     def prepare(self, data_search, data_prediction, n_categories, data_navigation=None) -> DeviceBucketLayout:
         """Build (once) the bucket-major device layout for ``data_search`` / ``data_prediction``."""
@@ -124,6 +129,7 @@ class LearnedIndex:
                                                     device=self.device)
         self._layout_key = key
         self._layout_refs = (data_search, data_prediction)  # keep ids from being recycled
+        self._graphs.clear()
         return self._layout
 
     # ------------------------------------------------------------------ navigation --
@@ -242,6 +248,55 @@ class LearnedIndex:
                               counts=counts)
         return dists, nns
 
+    # ------------------------------------------------------------------ CUDA graph --
+    def search_graphed(self, qn, qs, n_categories: List[int], n_buckets: int, k: int):
+        """``search_device`` as ONE CUDA-graph replay: the ~15 launches of a search (split, Linear
+        layers, softmax/top-n or tree navigation, inversion, scan, merge) are captured once per
+        (batch shape, budget) with static input/output buffers, so a small batch costs one graph
+        launch instead of ~15 host-side launches.  ``qn`` / ``qs`` may be host (numpy / pinned
+        torch) or device matrices; they are copied into the static inputs.  Returns
+        ``(dists, nns, stage_ms)`` -- the static output tensors, valid until the next replay of the
+        same shape, and the per-stage milliseconds of the eager run made at capture time."""
+        shared = qs is qn
+        def as_tensor(x):
+            if isinstance(x, torch.Tensor):
+                return x
+            a = np.asarray(x)
+            if a.dtype not in (np.float16, np.float32):
+                a = a.astype(np.float32)  # model.py:104
+            return torch.from_numpy(np.ascontiguousarray(a))
+        tn = as_tensor(qn)
+        ts = tn if shared else as_tensor(qs)
+        key = (tuple(tn.shape), tn.dtype, tuple(ts.shape), ts.dtype, shared, tuple(n_categories), int(n_buckets),
+               int(k), id(self._layout), self.scan_impl)
+        entry = self._graphs.get(key)
+        if entry is None:
+            if len(self._graphs) >= GRAPH_CACHE:
+                self._graphs.pop(next(iter(self._graphs)))
+            sn = torch.empty(tn.shape, dtype=tn.dtype, device=self.device)
+            ss = sn if shared else torch.empty(ts.shape, dtype=ts.dtype, device=self.device)
+            sn.copy_(tn, non_blocking=True)
+            if not shared:
+                ss.copy_(ts, non_blocking=True)
+            # eager run first: fills every lazy cache (weight splits, tensor-map driver entry point, the
+            # navigation tree) outside the capture and yields the per-stage timings
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            self.search_device(sn, ss, n_categories, n_buckets, k, events=ev)
+            torch.cuda.current_stream().synchronize()
+            stage_ms = [ev[j].elapsed_time(ev[j + 1]) for j in range(4)]
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                d, i = self.search_device(sn, ss, n_categories, n_buckets, k)
+            entry = dict(graph=graph, qn=sn, qs=ss, dists=d, nns=i, stage_ms=stage_ms, order=self.last_bucket_order)
+            self._graphs[key] = entry
+        else:
+            entry["qn"].copy_(tn, non_blocking=True)
+            if not shared:
+                entry["qs"].copy_(ts, non_blocking=True)
+        entry["graph"].replay()
+        self.last_bucket_order = entry["order"]
+        return entry["dists"], entry["nns"], entry["stage_ms"]
+
     def search(
         self,
         data_navigation,
@@ -267,16 +322,27 @@ class LearnedIndex:
             self.prepare(data_search, data_prediction, n_categories, data_navigation)
         assert self._layout is not None, "no index data: pass data_search/data_prediction or attach_layout()"
 
-        qn = to_device_matrix(queries_navigation, self.device)
-        qs = qn if queries_search is queries_navigation else to_device_matrix(queries_search, self.device)
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
-        dists_d, nns_d = self.search_device(qn, qs, n_categories, n_buckets, k, events=ev)
-        dists = dists_d.cpu().numpy()
-        nns = nns_d.cpu().numpy().view(np.uint32)
+        if 0 < len(queries_search) <= GRAPH_MAX_NQ and self.use_graphs:
+            # latency-bound batch sizes: one graph replay; the stage split reported is the one measured
+            # when this shape was captured, "search" is this call's wall time
+            dists_d, nns_d, st = self.search_graphed(
+                queries_navigation, queries_navigation if queries_search is queries_navigation else queries_search,
+                n_categories, n_buckets, k)
+            dists = dists_d.cpu().numpy()
+            nns = nns_d.cpu().numpy().view(np.uint32)
+            stage = [t / 1e3 for t in st]
+        else:
+            qn = to_device_matrix(queries_navigation, self.device)
+            qs = qn if queries_search is queries_navigation else to_device_matrix(queries_search, self.device)
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            dists_d, nns_d = self.search_device(qn, qs, n_categories, n_buckets, k, events=ev)
+            dists = dists_d.cpu().numpy()
+            nns = nns_d.cpu().numpy().view(np.uint32)
+            stage = [ev[j].elapsed_time(ev[j + 1]) / 1e3 for j in range(4)]
 
-        measured_time["inference"] = ev[0].elapsed_time(ev[1]) / 1e3
-        measured_time["search_within_buckets"] = ev[1].elapsed_time(ev[4]) / 1e3
-        measured_time["seq_search"] = ev[2].elapsed_time(ev[3]) / 1e3
-        measured_time["sort"] = ev[3].elapsed_time(ev[4]) / 1e3
+        measured_time["inference"] = stage[0]
+        measured_time["search_within_buckets"] = stage[1] + stage[2] + stage[3]
+        measured_time["seq_search"] = stage[2]
+        measured_time["sort"] = stage[3]
         measured_time["search"] = time.time() - s
         return dists, nns, measured_time

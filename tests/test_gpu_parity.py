@@ -449,3 +449,33 @@ def test_property_ragged_buckets_match_oracle():
                              what=f"seed={seed} C={C} nq={nq} d={d} B={B} k={k} sizes={sizes.tolist()}")
 
     run()
+
+
+def test_graph_replay_equals_eager_launches():
+    """`search` replays one CUDA graph per (shape, budget) for latency-bound batch sizes; results
+    must be bit-identical to the eager launches, also when the same graph is replayed with new
+    queries, and for a multi-level index."""
+    n, nq, C, B = 20_000, 333, 9, 3
+    X, Q, layers, pred = _synthetic(n, 2 * nq, C, steps=40)
+    li = _index(layers, C)
+    assert li.use_graphs
+    d1, i1, t1 = li.search(None, Q[:nq], X, Q[:nq], pred, [C], n_buckets=B, k=10)
+    d2, i2, _ = li.search(None, Q[nq:], X, Q[nq:], pred, [C], n_buckets=B, k=10)  # replay, new queries
+    assert len(li._graphs) == 1 and set(t1) >= {"inference", "search_within_buckets", "seq_search", "sort", "search"}
+    order2 = li.last_bucket_order.cpu().numpy().copy()
+    li.use_graphs = False
+    e1, j1, _ = li.search(None, Q[:nq], X, Q[:nq], pred, [C], n_buckets=B, k=10)
+    e2, j2, _ = li.search(None, Q[nq:], X, Q[nq:], pred, [C], n_buckets=B, k=10)
+    np.testing.assert_array_equal(d1, e1)
+    np.testing.assert_array_equal(i1, j1)
+    np.testing.assert_array_equal(d2, e2)
+    np.testing.assert_array_equal(i2, j2)
+    assert np.array_equal(order2, li.last_bucket_order.cpu().numpy())
+    assert not np.array_equal(i1, i2)
+    # other budgets / k get their own graph; nq == 1 works
+    li.use_graphs = True
+    d3, i3, _ = li.search(None, Q[:1], X, Q[:1], pred, [C], n_buckets=1)
+    li.use_graphs = False
+    e3, j3, _ = li.search(None, Q[:1], X, Q[:1], pred, [C], n_buckets=1)
+    np.testing.assert_array_equal(d3, e3)
+    np.testing.assert_array_equal(i3, j3)

@@ -61,3 +61,26 @@ for B in [int(x) for x in a.probes.split(",") if x]:
     run(10_000, B, True)
 for nq in [int(x) for x in a.batches.split(",") if x]:
     run(nq, 4, nq <= 10_000)
+
+
+def latency(nq, B=4, reps=30):
+    """Host-to-host latency of `LearnedIndex.search` (pinned host queries in, numpy out): one CUDA
+    graph replay vs the eager launches."""
+    import time
+    Qh = Qall[:nq].cpu().pin_memory()
+    out = {"nq": nq, "B": B, "what": "host-to-host search latency"}
+    for mode, flag in (("graph_ms", True), ("eager_ms", False)):
+        li.use_graphs = flag
+        ts = []
+        for r in range(5 + reps):
+            t0 = time.perf_counter()
+            li.search(None, Qh, None, Qh, None, [C], n_buckets=B, k=10)
+            ts.append(time.perf_counter() - t0)
+        out[mode] = float(np.median(ts[5:]) * 1e3)
+    li.use_graphs = True
+    print(json.dumps(out), flush=True)
+
+
+for nq in [int(x) for x in a.batches.split(",") if x]:
+    if nq <= 4096:
+        latency(nq)
