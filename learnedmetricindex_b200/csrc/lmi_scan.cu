@@ -203,6 +203,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                             ptx::mbar_arrive(&bars->full[stage]);
                             nb = 0;
                         } else {
+                            if (dbg & 4) nb = (nb + 1) / 2;  // ablation: half the operand traffic (stale boxes for the rest)
                             ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
                         }
                         for (int b = 0; b < nb; ++b)
