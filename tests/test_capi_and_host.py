@@ -109,3 +109,26 @@ def test_flat_bucket_ids_follow_groupby_key_order():
     bad = np.array([[0, -1, -1], [2, 3, 1], [3, 0, 0], [1, 4, 0]])
     assert flat_bucket_ids(bad, cats).tolist() == [24, 23, 24, 24]
     assert unflatten_bucket_ids(np.array([[5, -1]]), cats).tolist() == [[[0, 2, 1], [-1, -1, -1]]]
+
+
+def test_results_contract_roundtrip(tmp_path):
+    """store_results / get_recall / res.csv (search/search.py:51-63, eval/eval.py:37-77)."""
+    import csv
+    import numpy as np
+    from learnedmetricindex_b200 import results as res
+    from oracle import lmi_oracle as orc
+
+    rs = np.random.RandomState(0)
+    gt = np.stack([rs.permutation(500)[:10] + 1 for _ in range(40)]).astype(np.int64)
+    anns = gt.copy().astype(np.uint32)
+    anns[:, 7:] = 100_000 + np.arange(3)  # 7 of 10 right
+    dists = np.sort(rs.rand(40, 10), axis=1)
+    p = res.store_results(str(tmp_path / "result" / "run.h5"), "learned-index", "clip768", dists, anns, 1.5, 0.25,
+                          "4-of-120", "100K")
+    back = res.load_results(p)
+    assert back["algo"] == "learned-index" and back["size"] == "100K" and float(back["querytime"]) == 0.25
+    assert np.array_equal(back["knns"], anns) and back["knns"].dtype == np.uint32
+    assert res.get_recall(anns, gt, 10) == orc.get_recall(anns, gt, 10) == 0.7
+    out = res.write_res_csv([p], {"100K": gt}, str(tmp_path / "res.csv"))
+    rows = list(csv.DictReader(open(out)))
+    assert list(rows[0]) == res.RES_COLUMNS and float(rows[0]["recall"]) == 0.7
