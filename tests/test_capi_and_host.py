@@ -132,3 +132,21 @@ def test_results_contract_roundtrip(tmp_path):
     out = res.write_res_csv([p], {"100K": gt}, str(tmp_path / "res.csv"))
     rows = list(csv.DictReader(open(out)))
     assert list(rows[0]) == res.RES_COLUMNS and float(rows[0]["recall"]) == 0.7
+
+
+def test_build_configuration_expands_and_validates():
+    """search/li/BuildConfiguration.py:8-135."""
+    import pytest
+    from learnedmetricindex_b200.builder import BuildConfiguration, kmeans_gpu
+
+    c = BuildConfiguration(kmeans_gpu, 40, "MLP-3", 0.001, [5, 10])
+    assert c.n_levels == 2 and c.epochs == [40, 40] and c.model_types == ["MLP-3", "MLP-3"]
+    assert c.level_configurations[1] == (kmeans_gpu, "MLP-3", 40, 0.001, 10)
+    c2 = BuildConfiguration([kmeans_gpu], [40], ["MLP-3"], [0.001], [5, 10])
+    assert c2.level_configurations == c.level_configurations
+    with pytest.raises(AssertionError):
+        BuildConfiguration(kmeans_gpu, [40], "MLP-3", 0.001, [5, 10])  # mixed scalars and lists
+    with pytest.raises(AssertionError):
+        BuildConfiguration([kmeans_gpu], [40, 40, 40], ["MLP"], [0.1], [5, 10])
+    with pytest.raises(AssertionError):
+        BuildConfiguration(kmeans_gpu, 40, "MLP", 0.1, [])
