@@ -49,6 +49,8 @@ WORKLOADS = {
     "a": dict(n=100_000, nq=10_000, buckets=120, name="100k x 768 fp16, 120 buckets, MLP-4, 10k queries, k=10"),
     "b": dict(n=10_000_000, nq=10_000, buckets=120, name="10M x 768 fp16, 120 buckets, MLP-4, 10k queries, k=10"),
     "c": dict(n=100_000_000, nq=10_000, buckets=120, name="100M x 768 fp16, 120 buckets, MLP-4, 10k queries, k=10"),
+    # 2-level index (the reference CLI's default tree shape): see run_multilevel; --probe defaults to 10 of 100
+    "ml": dict(n=1_000_000, nq=10_000, buckets=100, name="1M x 768 fp16, n_categories [10, 10], 10k queries, k=10"),
 }
 D = 768
 K_NN = 10
@@ -375,6 +377,123 @@ def emit_json(obj):
         os.write(_REAL_STDOUT, line)
 
 
+
+# --------------------------------------------------------------------------------------
+# multi-level workload: `--workload ml`, single GPU
+# --------------------------------------------------------------------------------------
+def run_multilevel(args):
+    """The reference CLI's default tree shape (`--n-categories 10 10`, search/search.py:314) in the
+    notebook's arrangement: a low-dimensional navigation representation (PCA of the 768-d vectors,
+    search/search.py:192-216) routes through a 2-level tree of `MLP` models, the scan runs on the
+    768-d vectors.  Prints one JSON line: device-timed QPS, end-to-end QPS through
+    `LearnedIndex.search` with host queries, per-stage milliseconds, recall@10, and -- the
+    cpu_baseline leg -- the CPU oracle's QPS on a query sample with the agreement of the visit
+    order and ids on that sample."""
+    from learnedmetricindex_b200 import LearnedIndex
+    from learnedmetricindex_b200 import synthetic as syn
+    from learnedmetricindex_b200.layout import DeviceBucketLayout
+    from learnedmetricindex_b200.navigation import flat_bucket_ids
+
+    assert int(os.environ.get("WORLD_SIZE", "1")) == 1, "--workload ml is a single-GPU measurement"
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    cats, B = list(args.cats), args.probe
+
+    spec = syn.MixtureSpec()
+    X = syn.make_vectors(args.n, spec, device=dev)
+    Q = syn.make_vectors(args.nq, spec, device=dev, stream=1)
+    # navigation representation: PCA to nav_dim from a sample, re-normalised, stored fp16
+    g = torch.Generator(device=dev).manual_seed(7)
+    samp = X[torch.randperm(args.n, generator=g, device=dev)[:100_000]].float()
+    mean = samp.mean(0, keepdim=True)
+    _, _, V = torch.pca_lowrank(samp - mean, q=args.nav_dim, center=False, niter=4)
+    proj = lambda t: torch.nn.functional.normalize((t.float() - mean) @ V, dim=1).to(torch.float16)
+    Xn = torch.cat([proj(X[s : s + (1 << 20)]) for s in range(0, args.n, 1 << 20)])
+    Qn = proj(Q)
+    t0 = time.time()
+    root, internal, pred, bucket_paths = syn.build_standin_index_two_level(Xn, cats, args.ml_model_type)
+    log(f"stand-in 2-level build: {len(internal)} internal models, {len(bucket_paths)} buckets, {time.time() - t0:.1f}s")
+
+    to_np = syn.layers_to_numpy
+    li = LearnedIndex(to_np(root), {p: to_np(l) for p, l in internal.items()}, bucket_paths)
+    labels = torch.from_numpy(flat_bucket_ids(pred.cpu().numpy(), cats)).to(dev)
+    n_layout = int(np.prod(cats)) + int((labels == int(np.prod(cats))).any().item())
+    li.attach_layout(DeviceBucketLayout.from_device(X, labels, n_layout))
+    sizes = np.diff(li._layout.bucket_off_host)
+    log(f"bucket sizes: min {sizes.min()} max {sizes.max()}")
+
+    # exact ground truth for recall
+    gt = torch.empty((args.nq, 10), dtype=torch.int64, device=dev)
+    for s in range(0, args.nq, 1000):
+        best_v = torch.full((min(1000, args.nq - s), 10), -2.0, device=dev)
+        best_i = torch.zeros((min(1000, args.nq - s), 10), dtype=torch.int64, device=dev)
+        for r in range(0, args.n, 1 << 20):
+            sim = Q[s : s + 1000].float() @ X[r : r + (1 << 20)].float().t()
+            v, i = sim.topk(10, dim=1)
+            allv, alli = torch.cat([best_v, v], 1), torch.cat([best_i, i + r + 1], 1)
+            best_v, sel = allv.topk(10, dim=1)
+            best_i = torch.gather(alli, 1, sel)
+        gt[s : s + 1000] = best_i
+    gt = gt.cpu().numpy()
+
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    stage = np.zeros(4)
+    for it in range(args.warmup + args.steps):
+        if it == args.warmup:
+            torch.cuda.synchronize()
+            t_start = torch.cuda.Event(enable_timing=True)
+            t_start.record()
+        d_dev, i_dev = li.search_device(Qn, Q, cats, B, 10, events=ev)
+        if it >= args.warmup:
+            torch.cuda.synchronize()
+            stage += [ev[j].elapsed_time(ev[j + 1]) for j in range(4)]
+    t_end = torch.cuda.Event(enable_timing=True)
+    t_end.record()
+    torch.cuda.synchronize()
+    ms = t_start.elapsed_time(t_end) / args.steps
+    stage /= args.steps
+    nns = i_dev.cpu().numpy().view(np.uint32).astype(np.int64)
+    recall = float(np.mean([len(set(a) & set(b)) for a, b in zip(nns, gt)]) / 10)
+
+    Qn_h, Q_h = Qn.cpu().numpy(), Q.cpu().numpy()
+    e2e = []
+    for it in range(3 + 10):
+        t0 = time.perf_counter()
+        d_h, i_h, _ = li.search(None, Qn_h, None, Q_h, None, cats, n_buckets=B, k=10)
+        e2e.append(time.perf_counter() - t0)
+    e2e_ms = float(np.median(e2e[3:]) * 1e3)
+
+    cpu = parity = None
+    if not args.no_cpu_baseline:  # the cpu_baseline leg: the oracle as checker and as the timed CPU path
+        from oracle import lmi_oracle as orc
+
+        nc = min(args.ml_cpu_queries, args.nq)
+        lay = orc.BucketMajor(X.cpu().numpy().astype(np.float32), pred.cpu().numpy())
+        idx = orc.OracleIndex(to_np(root), {p: to_np(l) for p, l in internal.items()}, bucket_paths)
+        t0 = time.time()
+        exp_d, exp_i, _, exp_order = orc.search(idx, Qn_h[:nc], None, Q_h[:nc], None, cats, n_buckets=B, k=10,
+                                                layout=lay)
+        cpu_s = time.time() - t0
+        got_paths, _ = li._precompute_bucket_order(Qn_h[:nc], B, cats)
+        same = (got_paths == exp_order).all(axis=(1, 2))
+        cpu = {"value": nc / cpu_s, "unit": "QPS", "kind": "port", "cores": torch.get_num_threads(),
+               "sample": f"first {nc} queries, oracle/lmi_oracle.py, vectors pre-widened to f32"}
+        parity = {"visit_order_rows_equal": float(same.mean()),
+                  "id_agreement_on_equal_rows": float((i_h[:nc][same] == exp_i[same]).mean())}
+
+    emit_json({
+        "metric": "QPS, 2-level LMI", "value": args.nq / ms * 1e3, "unit": "QPS", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "data": "synthetic",
+        "dtype": "f16 in / f32 accumulate (scan), tf32 x3 split / f32 accumulate (MLPs)",
+        "config": {"workload": f"{args.n} x 768 fp16, n_categories {cats}, {args.ml_model_type} models on a "
+                               f"{args.nav_dim}-d PCA navigation representation, {args.nq} queries, "
+                               f"{B} of {len(bucket_paths)} buckets, k=10", "recall_at_10": recall},
+        "kernel_ms": {"navigation": stage[0], "invert": stage[1], "scan": stage[2], "merge": stage[3]},
+        "e2e": {"value": args.nq / e2e_ms * 1e3, "unit": "QPS", "ms_per_step": e2e_ms},
+        "cpu_baseline": cpu, "parity_vs_oracle": parity,
+    })
+
+
 def main():
     global _REAL_STDOUT
     sys.stdout.flush()
@@ -389,7 +508,8 @@ def main():
     ap.add_argument("--n", type=int, default=0)
     ap.add_argument("--nq", type=int, default=0)
     ap.add_argument("--buckets", type=int, default=0)
-    ap.add_argument("--probe", type=int, default=4, help="buckets probed per query (B); 0 = smallest B with recall>=0.90")
+    ap.add_argument("--probe", type=int, default=None,
+                    help="buckets probed per query (B); default 4 (10 for --workload ml); 0 = smallest B with recall>=0.90")
     ap.add_argument("--train-steps", type=int, default=300)
     ap.add_argument("--centres", type=int, default=2000)
     ap.add_argument("--noise", type=float, default=0.25)
@@ -397,7 +517,13 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", default="", help="comma list of B values: print recall/QPS per B to stderr")
+    ap.add_argument("--cats", type=int, nargs=2, default=[10, 10], help="--workload ml: n_categories")
+    ap.add_argument("--nav-dim", type=int, default=96, help="--workload ml: PCA navigation dimensionality")
+    ap.add_argument("--ml-model-type", default="MLP", help="--workload ml: model type of every tree node")
+    ap.add_argument("--ml-cpu-queries", type=int, default=2000, help="--workload ml: queries of the cpu_baseline leg")
     args = ap.parse_args()
+    if args.probe is None:
+        args.probe = 10 if args.workload == "ml" else 4
     wl = WORKLOADS[args.workload]
     args.n = args.n or wl["n"]
     args.nq = args.nq or wl["nq"]
@@ -410,6 +536,9 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
+    if args.workload == "ml":
+        assert args.impl == "ours", "the multi-level workload has no reference arm (its cpu_baseline leg times the oracle)"
+        return run_multilevel(args)
     if args.impl == "reference":
         return run_reference(args, wl_name, rank, world, local_rank)
 
