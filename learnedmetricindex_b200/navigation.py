@@ -9,9 +9,11 @@ model on the queries that popped it (one ``predict_proba`` per internal model pe
 and pushes every child with the child's RAW probability.  A node's probability is a pure
 function of (model, query), so the GPU form is
 
-1. dense grouped inference: every internal model is evaluated on the whole query batch
-   (``NeuralNetwork.logits`` -> ``lmi_softmax_probs``) into one table
-   ``node_prob f32[nq, n_nodes]`` with a column per tree node (breadth-first numbering);
+1. dense grouped inference: every internal model is evaluated on the whole query batch into one
+   table ``node_prob f32[nq, n_nodes]`` with a column per tree node (breadth-first numbering) --
+   all models of a tree level per launch (``lmi_linear_tc`` on the stacked first layers,
+   ``lmi_linear_tc_grouped`` after, ``lmi_softmax_segments`` in place), or one launch set per
+   model (``NeuralNetwork.logits`` -> ``lmi_softmax_probs``) when a level is not uniform;
 2. ``lmi_navigate_tree``: one warp per query replays the best-first search over that table
    with the frontier in shared memory and writes the flat bucket ids in visiting order.
 
@@ -117,6 +119,7 @@ class NavigationTree:
         self.seg_start = torch.tensor(seg_start, dtype=torch.int32, device=self.device)
         self.seg_len = torch.tensor(seg_len, dtype=torch.int32, device=self.device)
         self._groups = self._stack_levels(by_depth)
+        self._root_stack = None  # the root's layers in the stacked-level format (built on first use)
 
     def _flat(self, prefix: Sequence[int]) -> int:
         f = 0
@@ -208,7 +211,7 @@ class NavigationTree:
         table = torch.empty((nq, self.n_nodes), dtype=torch.float32, device=self.device)
         root = self.root_model
         parts = root.split_input(qn)
-        if getattr(self, "_root_stack", None) is None:
+        if self._root_stack is None:
             self._root_stack = [dict(W=W, b=b, parts=None, in_dim=W.shape[1], out_dim=W.shape[0])
                                 for W, b in root.layers]
         self._forward_into_table(parts, root.input_dim, 1, self._root_stack, table, 0, root._split)

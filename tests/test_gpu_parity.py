@@ -420,6 +420,7 @@ def test_property_ragged_buckets_match_oracle():
     """Hypothesis over ragged bucket sizes (incl. s_b < 10 and empty buckets), query counts that
     leave partial tiles, B = 1 .. C, k <= 10 and odd dimensionalities."""
     from hypothesis import given, settings, strategies as st, HealthCheck
+    from learnedmetricindex_b200 import DeviceBucketLayout
     from tests.golden_util import seeded_layers
 
     @settings(max_examples=30, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
@@ -440,7 +441,7 @@ def test_property_ragged_buckets_match_oracle():
         layers = seeded_layers(seed + 5, "MLP-8", d, C, scale=4.0)
         ids = rs.permutation(np.arange(7, 7 + n))
         li = _index(layers, C)
-        li.attach_layout(__import__("learnedmetricindex_b200").DeviceBucketLayout.from_host(X, pred[:, 0], C, ids=ids))
+        li.attach_layout(DeviceBucketLayout.from_host(X, pred[:, 0], C, ids=ids))
         dd, ii, _ = li.search(None, Q, None, Q, None, [C], n_buckets=B, k=k)
         exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=k, ids=ids)
         probs, _ = orc.predict_proba(layers, orc.to_f32_tensor(Q))
