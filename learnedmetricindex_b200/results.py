@@ -14,7 +14,7 @@ from __future__ import annotations
 import csv
 import os
 from pathlib import Path
-from typing import Dict, Iterable, Optional
+from typing import Dict, Iterable
 
 import numpy as np
 
