@@ -220,6 +220,16 @@ int lmi_merge_ranks(const double *dists_all, const uint32_t *nns_all, int64_t ra
                     int64_t rank_stride_i, int world, int nq, int k,
                     double *dists, uint32_t *nns, void *stream);
 
+/* The exchange step fused with the merge: instead of an all-gather followed by lmi_merge_ranks,
+ * every rank reads its peers' result blocks straight out of peer memory (NVLink P2P through
+ * NVSwitch) inside the merge kernel.  rank_base: DEVICE array of `world` pointers, entry w = the
+ * address IN THIS PROCESS of rank w's packed block [dists f64[nq,k] | pad | nns u32[nq,k]]
+ * (symmetric memory / CUDA IPC mapping); nns_offset_bytes = offset of the nns part in a block.
+ * The caller orders the launch after a cross-rank barrier (all blocks written) and must not
+ * overwrite its own block until every peer has passed the next barrier (double buffering). */
+int lmi_merge_ranks_peer(const void *const *rank_base, int64_t nns_offset_bytes, int world, int nq,
+                         int k, double *dists, uint32_t *nns, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -256,6 +256,59 @@ __global__ void merge_ranks_kernel(const double* __restrict__ d_all, const uint3
     }
 }
 
+// The exchange step and the merge in ONE launch: rank w's packed block [dists f64[nq,k] | nns u32[nq,k]]
+// is read straight out of PEER memory (rank_base[w] is that rank's symmetric-memory buffer mapped into
+// this process: NVLink P2P loads through NVSwitch), staged per warp in shared memory with every lane
+// issuing independent remote loads, then merged as in merge_ranks_kernel.
+__global__ void merge_ranks_peer_kernel(const void* const* __restrict__ rank_base, int64_t nns_off, int world, int nq,
+                                        int k, double* __restrict__ dists, uint32_t* __restrict__ nns) {
+    extern __shared__ double peer_sm[];
+    const int warps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * warps + warp;
+    if (q >= nq) return;
+    const int per = world * k;
+    double* sd = peer_sm + (size_t)warp * per;
+    uint32_t* si = reinterpret_cast<uint32_t*>(peer_sm + (size_t)warps * per) + (size_t)warp * per;
+    for (int idx = lane; idx < per; idx += 32) {
+        const int w = idx / k, j = idx - w * k;
+        const char* base = static_cast<const char*>(rank_base[w]);
+        sd[idx] = reinterpret_cast<const double*>(base)[(size_t)q * k + j];
+        si[idx] = reinterpret_cast<const uint32_t*>(base + nns_off)[(size_t)q * k + j];
+    }
+    __syncwarp();
+    int head = 0;
+    bool live = lane < world;
+    double hv = live ? sd[lane * k] : INFINITY;
+    for (int t = 0; t < k; ++t) {
+        double kd = hv;
+        int ke = live ? lane : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double od = __shfl_xor_sync(0xffffffffu, kd, o);
+            const int oe = __shfl_xor_sync(0xffffffffu, ke, o);
+            if (oe != 0x7fffffff && (ke == 0x7fffffff || od < kd || (od == kd && oe < ke))) {
+                kd = od;
+                ke = oe;
+            }
+        }
+        if (ke == 0x7fffffff) {
+            if (lane == 0) {
+                dists[(size_t)q * k + t] = INFINITY;
+                nns[(size_t)q * k + t] = 0u;
+            }
+            continue;
+        }
+        if (lane == ke) {
+            dists[(size_t)q * k + t] = hv;
+            nns[(size_t)q * k + t] = si[lane * k + head];
+            ++head;
+            if (head < k) hv = sd[lane * k + head];
+            else live = false;
+        }
+    }
+}
+
 }  // namespace lmi
 
 extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, const int32_t* slot_of_pair,
@@ -296,5 +349,18 @@ extern "C" int lmi_merge_ranks(const double* dists_all, const uint32_t* nns_all,
     const int warps = 4;
     lmi::merge_ranks_kernel<<<(nq + warps - 1) / warps, warps * 32, 0, st>>>(dists_all, nns_all, rank_stride_d,
                                                                            rank_stride_i, world, nq, k, dists, nns);
+    return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lmi_merge_ranks_peer(const void* const* rank_base, int64_t nns_offset_bytes, int world, int nq, int k,
+                                    double* dists, uint32_t* nns, void* stream) {
+    if (!rank_base || !dists || !nns || world <= 0 || nq < 0 || k <= 0 || nns_offset_bytes < 0) return LMI_E_BADARG;
+    if (world > 32 || (nns_offset_bytes & 3)) return LMI_E_UNSUPPORTED;
+    if (nq == 0) return 0;
+    const int warps = 4;
+    const size_t smem = (size_t)warps * world * k * (sizeof(double) + sizeof(uint32_t));
+    if (smem > 48 * 1024) return LMI_E_UNSUPPORTED;
+    lmi::merge_ranks_peer_kernel<<<(nq + warps - 1) / warps, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+        rank_base, nns_offset_bytes, world, nq, k, dists, nns);
     return static_cast<int>(cudaGetLastError());
 }

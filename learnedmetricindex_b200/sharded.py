@@ -83,6 +83,52 @@ class GatherBuffers:
         return self.per_rank // 4
 
 
+class PeerBuffers:
+    """The exchange step over PEER MEMORY instead of a collective: every rank's packed result block
+    ``[nq*k f64 | nq*k u32]`` lives in a symmetric-memory buffer (``torch.distributed.
+    _symmetric_memory``: the same allocation mapped into every process of the box over NVLink), the
+    local merge kernel writes straight into it, a cross-rank barrier orders the step, and
+    ``lmi_merge_ranks_peer`` reads all peers' blocks through NVSwitch inside the merge kernel --
+    all-gather and k-way merge in one launch.  Two blocks alternate so a rank may start the next
+    search while slower peers still read its previous results (one barrier per search)."""
+
+    def __init__(self, nq: int, k: int, world: int, rank: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.nq, self.k, self.world, self.rank = nq, k, world, rank
+        self.bytes_d = nq * k * 8
+        self.bytes_i = nq * k * 4
+        self.per_rank = -(-(self.bytes_d + self.bytes_i) // 16) * 16
+        self.blocks, self.handles = [], []
+        for _ in range(2):
+            t = symm_mem.empty(self.per_rank, dtype=torch.uint8, device=device)
+            t.zero_()
+            self.handles.append(symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD))
+            self.blocks.append(t)
+        self.turn = 0
+
+    def local_views(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        blk = self.blocks[self.turn]
+        d = blk[: self.bytes_d].view(torch.float64).view(self.nq, self.k)
+        i = blk[self.bytes_d : self.bytes_d + self.bytes_i].view(torch.int32).view(self.nq, self.k)
+        return d, i
+
+    def exchange_and_merge(self):
+        from . import _native
+
+        hdl = self.handles[self.turn]
+        dev = self.blocks[0].device
+        out_d = torch.empty((self.nq, self.k), dtype=torch.float64, device=dev)
+        out_i = torch.empty((self.nq, self.k), dtype=torch.int32, device=dev)
+        hdl.barrier(channel=0)  # every rank's block of this turn is written (device-side, on this stream)
+        _native.check(_native.lib().lmi_merge_ranks_peer(hdl.buffer_ptrs_dev, self.bytes_d, self.world, self.nq,
+                                                         self.k, out_d.data_ptr(), out_i.data_ptr(),
+                                                         torch.cuda.current_stream().cuda_stream),
+                      "lmi_merge_ranks_peer")
+        self.turn ^= 1
+        return out_d, out_i
+
+
 def merge_ranks_device(buf: GatherBuffers, out_d: torch.Tensor, out_i: torch.Tensor) -> None:
     """``lmi_merge_ranks`` over the gathered buffer (CUDA)."""
     from . import _native
@@ -133,18 +179,26 @@ class ShardedLearnedIndex:
     owns (``DeviceBucketLayout.restrict_to_buckets`` or a layout built from the local rows).
     """
 
-    def __init__(self, local, group=None, shard_navigation: bool = True):
+    def __init__(self, local, group=None, shard_navigation: bool = True, exchange: Optional[str] = None):
+        import os
+
         self.local = local
         self.group = group
         self.shard_navigation = shard_navigation  # MLP + top-B on nq/world queries per rank, then all-gather
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
+        # "peer": results are exchanged by reading peer memory inside the merge kernel (PeerBuffers);
+        # "nccl": all-gather + lmi_merge_ranks (GatherBuffers; also what the gloo tests run)
+        self.exchange = exchange or os.environ.get("LMI_EXCHANGE", "peer")
         self._bufs = {}
 
-    def _buffers(self, nq: int, k: int, device) -> GatherBuffers:
+    def _buffers(self, nq: int, k: int, device):
         key = (nq, k)
         if key not in self._bufs:
-            self._bufs[key] = GatherBuffers(nq, k, self.world, self.rank, device)
+            if self.exchange == "peer" and torch.device(device).type == "cuda" and self.world > 1:
+                self._bufs[key] = PeerBuffers(nq, k, self.world, self.rank, device, self.group)
+            else:
+                self._bufs[key] = GatherBuffers(nq, k, self.world, self.rank, device)
         return self._bufs[key]
 
     def search_device(self, qn, qs, n_categories, n_buckets: int, k: int, events=None):
@@ -162,6 +216,8 @@ class ShardedLearnedIndex:
             order = gather_bucket_order(local_order, nq, int(n_buckets), self.group)
         self.local.search_device(qn, qs, n_categories, n_buckets, k, events=events, out=buf.local_views(),
                                  bucket_order=order)
+        if isinstance(buf, PeerBuffers):
+            return buf.exchange_and_merge()
         return gather_and_merge(buf, self.group)
 
     def _upload_sharded(self, host_matrix, dev) -> torch.Tensor:

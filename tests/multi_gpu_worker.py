@@ -1,0 +1,53 @@
+"""Worker of tests/test_gpu_multi.py (run under torchrun, one process per GPU): the bucket-sharded
+search with both exchange paths -- peer-memory merge (lmi_merge_ranks_peer) and NCCL all-gather +
+lmi_merge_ranks -- must equal the unsharded search on the same index, bit for bit."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=dev)
+    from learnedmetricindex_b200 import DeviceBucketLayout, LearnedIndex
+    from learnedmetricindex_b200 import synthetic as syn
+    from learnedmetricindex_b200.sharded import ShardedLearnedIndex, partition_buckets
+
+    n, nq, C = 40_000, 1000, 16
+    spec = syn.MixtureSpec(n_centres=300)
+    X = syn.make_vectors(n, spec)  # CPU generator: identical on every rank
+    Q = syn.make_vectors(nq, spec, stream=1).to(dev)
+    layers, pred = syn.build_standin_index(X, C, steps=60)
+    layers = syn.layers_to_numpy(layers)
+    full = DeviceBucketLayout.from_host(X.numpy(), pred.numpy()[:, 0], C, device=dev)
+    parts = partition_buckets(np.diff(full.bucket_off_host), world)
+    ref = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+    ref.attach_layout(full)
+    for B, k in [(1, 10), (3, 10), (5, 7)]:
+        exp_d, exp_i = ref.search_device(Q, Q, [C], B, k)
+        for exchange in ("peer", "nccl"):
+            li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+            li.attach_layout(full.restrict_to_buckets(parts[rank]))
+            eng = ShardedLearnedIndex(li, exchange=exchange)
+            for rep in range(3):  # repeated: the peer path alternates between its two blocks
+                d, i = eng.search_device(Q, Q, [C], B, k)
+                assert torch.equal(d, exp_d) and torch.equal(i, exp_i), (exchange, B, k, rep, rank)
+            # host-facing API (queries uploaded 1/world per rank and all-gathered)
+            dh, ih, _ = eng.search(None, Q.cpu().numpy(), None, Q.cpu().numpy(), None, [C], n_buckets=B, k=k)
+            assert np.array_equal(dh, exp_d.cpu().numpy()) and np.array_equal(ih.view(np.int32), exp_i.cpu().numpy())
+    dist.barrier()
+    if rank == 0:
+        print("MULTI_GPU_OK", world)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
