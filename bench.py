@@ -591,6 +591,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_enqueue_ms = [0.0]
+
     def timed_device_loop(Bp, steps, warmup, collect_scan=True):
         evs = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(steps)]
         for _ in range(warmup):
@@ -602,6 +604,7 @@ def main():
         for s in range(steps):
             engine.search_device(Q, Q, [C], Bp, K_NN, events=evs[s])
         e1.record()
+        host_enqueue_ms[0] = (time.time() - t_a) * 1e3 / steps  # host time to enqueue one step's launches
         barrier()
         t_b = time.time()
         total_ms = e0.elapsed_time(e1)
@@ -626,6 +629,7 @@ def main():
     total_ms, scan_ms, parts, win_dev = timed_device_loop(B, K, W)
     ms_per_step = total_ms / K
     value = nq / (ms_per_step / 1e3)
+    host_ms_main = host_enqueue_ms[0]
 
     # ---- end to end: host queries (pinned) -> search() -> host results, every step ----
     Qh = torch.empty(Q.shape, dtype=Q.dtype).pin_memory()
@@ -742,6 +746,7 @@ def main():
         "e2e": {"value": e2e_qps, "unit": "QPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_s / K * 1e3},
         "gpu_launches": launches_per_step * K,
+        "host_enqueue_ms_per_step": host_ms_main,
         "kernel_ms": parts,
         "roofline": roof,
         "cpu_baseline": cpu,
