@@ -217,8 +217,18 @@ def build_workload(args, device, rank, world, use_repo_kernels=True):
 
     from learnedmetricindex_b200.sharded import owner_of_bucket, partition_buckets
 
-    # queries follow the data distribution, so a bucket's scan work (probes x rows) goes like size^2
-    parts = partition_buckets(sizes_h, world, weights=sizes_h)
+    # Balance the ranks' SCAN WORK, not their bytes: a bucket costs rows x (probing queries rounded up to
+    # the scan's 128-query tiles).  The expected probes per bucket come from a calibration batch drawn
+    # from the data distribution (its own random stream, NOT the timed queries), routed by the index.
+    weights = sizes_h.astype(np.float64)  # fallback: queries follow the data, so work goes like size^2
+    probe = int(getattr(args, "probe", 0) or 0)
+    if world > 1 and use_repo_kernels and probe > 0:
+        qcal = syn.make_vectors(nq, spec, device=device, stream=2)
+        order_cal, _ = net.topn_device(qcal, min(probe, C))
+        m_b = torch.bincount(order_cal.reshape(-1).to(torch.int64), minlength=C).cpu().numpy()
+        weights = 128.0 * np.ceil(np.maximum(m_b, 1) / 128.0)
+        del qcal, order_cal
+    parts = partition_buckets(sizes_h, world, weights=weights)
     own = torch.from_numpy(owner_of_bucket(parts, C)).to(device)
     local_sizes = np.where(owner_of_bucket(parts, C) == rank, sizes_h, 0)
     off = np.zeros(C + 1, dtype=np.int64)
@@ -615,6 +625,10 @@ def main():
             t = torch.tensor([total_ms], device=device, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             total_ms = float(t.item())
+            per_rank = torch.zeros(world, device=device, dtype=torch.float64)
+            per_rank[rank] = parts["scan"]
+            dist.all_reduce(per_rank)
+            parts["scan_per_rank"] = [round(v, 4) for v in per_rank.tolist()]
         return total_ms, scan_ms, parts, (t_a, t_b)
 
     if args.sweep:
