@@ -229,8 +229,18 @@ def build_workload(args, device, rank, world, use_repo_kernels=True):
         weights = 128.0 * np.ceil(np.maximum(m_b, 1) / 128.0)
         del qcal, order_cal
     parts = partition_buckets(sizes_h, world, weights=weights)
-    own = torch.from_numpy(owner_of_bucket(parts, C)).to(device)
-    local_sizes = np.where(owner_of_bucket(parts, C) == rank, sizes_h, 0)
+    # this rank's slice [lo, hi) of every bucket's rows (in bucket order): the whole bucket or nothing when
+    # whole buckets are assigned to ranks; an equal 1/world slice of EVERY bucket with --shard rows (every
+    # rank then has the same buckets, probes and tile structure: perfectly balanced scan work)
+    if getattr(args, "shard", "buckets") == "rows" and world > 1:
+        lo_h = sizes_h * rank // world
+        hi_h = sizes_h * (rank + 1) // world
+    else:
+        mine_h = owner_of_bucket(parts, C) == rank
+        lo_h = np.zeros(C, dtype=np.int64)
+        hi_h = np.where(mine_h, sizes_h, 0)
+    local_sizes = hi_h - lo_h
+    lo_d, hi_d = torch.from_numpy(lo_h).to(device), torch.from_numpy(hi_h).to(device)
     off = np.zeros(C + 1, dtype=np.int64)
     off[1:] = np.cumsum(local_sizes)
     n_local = int(off[-1])
@@ -248,9 +258,10 @@ def build_workload(args, device, rank, world, use_repo_kernels=True):
     for ci, (s, m) in enumerate(plan):
         x = make_chunk(ci, m, spec, device)
         lab = preds[ci].to(torch.int64)
-        mine = own[lab] == rank
-        rk, counts = stable_rank_in_group(torch.where(mine, lab, torch.full_like(lab, C)), C + 1)
-        dest = off_d[lab.clamp(max=C - 1)] + filled[lab] + rk
+        rk, counts = stable_rank_in_group(lab, C + 1)
+        pos = filled[lab] + rk  # position of the row inside its bucket (all ranks agree)
+        mine = (pos >= lo_d[lab]) & (pos < hi_d[lab])
+        dest = off_d[lab] + pos - lo_d[lab]
         sel = torch.nonzero(mine).reshape(-1)
         if sel.numel():
             dsel = dest[sel].contiguous()
@@ -526,6 +537,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", default="", help="comma list of B values: print recall/QPS per B to stderr")
+    ap.add_argument("--shard", default="buckets", choices=["buckets", "rows"],
+                    help="multi-GPU: whole buckets per rank (calibrated LPT) or an equal row slice of every bucket")
     ap.add_argument("--cats", type=int, nargs=2, default=[10, 10], help="--workload ml: n_categories")
     ap.add_argument("--nav-dim", type=int, default=96, help="--workload ml: PCA navigation dimensionality")
     ap.add_argument("--ml-model-type", default="MLP", help="--workload ml: model type of every tree node")
@@ -753,7 +766,8 @@ def main():
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f16 in / f32 accumulate (scan), tf32 x3 split / f32 accumulate (MLP)", "data": "synthetic",
         "config": {"workload": wl_name, "n": args.n, "nq": nq, "d": D, "n_buckets_in_index": C, "probed_buckets": B,
-                   "k": K_NN, "recall_at_10": recall, "sharding": f"buckets over {world} GPU(s)",
+                   "k": K_NN, "recall_at_10": recall, "sharding": (f"equal row slices of every bucket over {world} GPU(s)" if args.shard == "rows" and world > 1
+                                else f"buckets over {world} GPU(s)"),
                    "l2_policy": "inputs larger than L2 (bucket vectors %.1f GB per GPU, read once per step)"
                                 % (w["vectors"].numel() * 2 / 1e9),
                    "synthetic": {"centres": args.centres, "latent_dim": args.latent, "noise": args.noise}},
