@@ -537,13 +537,19 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", default="", help="comma list of B values: print recall/QPS per B to stderr")
-    ap.add_argument("--shard", default="buckets", choices=["buckets", "rows"],
-                    help="multi-GPU: whole buckets per rank (calibrated LPT) or an equal row slice of every bucket")
+    ap.add_argument("--shard", default="auto", choices=["auto", "buckets", "rows"],
+                    help="multi-GPU: whole buckets per rank (calibrated LPT) or an equal row slice of every bucket; "
+                         "auto = rows when a slice still holds >= 4 scan ranges of 16384 rows, else buckets")
     ap.add_argument("--cats", type=int, nargs=2, default=[10, 10], help="--workload ml: n_categories")
     ap.add_argument("--nav-dim", type=int, default=96, help="--workload ml: PCA navigation dimensionality")
     ap.add_argument("--ml-model-type", default="MLP", help="--workload ml: model type of every tree node")
     ap.add_argument("--ml-cpu-queries", type=int, default=2000, help="--workload ml: queries of the cpu_baseline leg")
     args = ap.parse_args()
+    if args.shard == "auto":
+        w_ = int(os.environ.get("WORLD_SIZE", "1"))
+        n_ = args.n or WORKLOADS[args.workload]["n"]
+        c_ = args.buckets or WORKLOADS[args.workload]["buckets"]
+        args.shard = "rows" if w_ > 1 and n_ // (w_ * c_) >= 4 * 16384 else "buckets"
     if args.probe is None:
         args.probe = 10 if args.workload == "ml" else 4
     wl = WORKLOADS[args.workload]
