@@ -151,3 +151,22 @@ class DeviceBucketLayout:
             vec = torch.zeros((1, self.d), dtype=torch.float16, device=self.device)[:0]
         return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths,
                                   d_data=self.d_data)
+
+    def restrict_to_slice(self, rank: int, world: int) -> "DeviceBucketLayout":
+        """Shard: keep rows ``[s_b*rank//world, s_b*(rank+1)//world)`` of EVERY bucket -- every rank
+        then scans the same buckets for the same probes with 1/world of the rows (perfectly balanced).
+        Valid for ``k <= 10``: an object ranked beyond 10 inside its bucket cannot reach the overall
+        top 10, so merging the ranks' lists gives the unsharded result (filler ids of undersized
+        buckets excepted)."""
+        off = self.bucket_off_host
+        sizes = np.diff(off)
+        lo = off[:-1] + sizes * rank // world
+        hi = off[:-1] + sizes * (rank + 1) // world
+        new_off = np.zeros(self.n_buckets + 1, dtype=np.int64)
+        new_off[1:] = np.cumsum(hi - lo)
+        rows = [torch.arange(a, b, device=self.device) for a, b in zip(lo.tolist(), hi.tolist()) if b > a]
+        sel = torch.cat(rows) if rows else torch.zeros(0, dtype=torch.int64, device=self.device)
+        vec = self.vectors[sel].contiguous() if sel.numel() else \
+            torch.zeros((1, self.d), dtype=torch.float16, device=self.device)[:0]
+        return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths,
+                                  d_data=self.d_data)

@@ -43,6 +43,16 @@ def main():
             # host-facing API (queries uploaded 1/world per rank and all-gathered)
             dh, ih, _ = eng.search(None, Q.cpu().numpy(), None, Q.cpu().numpy(), None, [C], n_buckets=B, k=k)
             assert np.array_equal(dh, exp_d.cpu().numpy()) and np.array_equal(ih.view(np.int32), exp_i.cpu().numpy())
+    # equal row slices of every bucket: same result for k <= 10 (distances always; ids on real candidates)
+    li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+    li.attach_layout(full.restrict_to_slice(rank, world))
+    eng = ShardedLearnedIndex(li)
+    for B, k in [(1, 10), (4, 10), (3, 5)]:
+        exp_d, exp_i = ref.search_device(Q, Q, [C], B, k)
+        d, i = eng.search_device(Q, Q, [C], B, k)
+        assert torch.equal(d, exp_d), ("rows", B, k, rank)
+        real = exp_d < 1e38
+        assert torch.equal(i[real], exp_i[real]), ("rows ids", B, k, rank)
     dist.barrier()
     if rank == 0:
         print("MULTI_GPU_OK", world)
