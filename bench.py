@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the LMI query path (``LearnedIndex.search``) on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload b|a|c]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload b|a|c|ml]
 
 A *step* is one pass of the hot path over one batch: MLP -> top-B buckets -> inversion ->
 bucket scan with fused top-10 -> merge (-> all-gather + rank merge when N > 1) for all
@@ -10,11 +10,15 @@ bucket scan with fused top-10 -> merge (-> all-gather + rank merge when N > 1) f
 Workloads (BASELINE.json ``configs``):
   b (default)  10M x 768 fp16, 120 buckets, MLP-4 (768->512->120), 10k queries, k=10, B=4  -- headline
   a            100k x 768, otherwise as b (the reference's CPU-runnable size)
-  c            100M x 768 sharded over N >= 2 GPUs
+  c            100M x 768 (153.6 GB: fits one B200; the sharded configuration for N = 2/4/8)
+  ml           1M x 768, 2-level index [10, 10] with a 96-d PCA navigation representation, 10 of 100
+               buckets (single GPU; see run_multilevel)
 
-``--gpus N`` (launched under torchrun, one rank per GPU) shards the buckets of the SAME
-workload over the N ranks ("strong" scaling): every rank scans its own buckets for the
-whole query batch, then one NCCL all-gather of the per-rank [nq,k] lists and a device merge.
+``--gpus N`` (launched under torchrun, one rank per GPU) shards the SAME workload over the N ranks
+("strong" scaling): whole buckets per rank (LPT on rows^2), or -- when a 1/N slice of a bucket still
+holds several scan ranges (``--shard``, automatic for 100M) -- an equal row slice of every bucket.
+Every rank scans its rows for the whole query batch; the exchange step reads the peers' [nq,k]
+lists out of peer memory inside the merge kernel (``LMI_EXCHANGE=nccl``: all-gather + merge).
 
 Printed JSON (one line, rank 0): ``value`` = device-timed QPS with inputs resident in HBM;
 ``e2e`` = QPS through ``LearnedIndex.search`` with HOST queries (pinned) -> H2D -> kernels ->
@@ -22,6 +26,10 @@ D2H of (dists, nns); ``roofline`` for the scan kernel (CUDA events around that l
 algorithmic flops/bytes as in DESIGN.md); ``cpu_baseline`` = the CPU oracle
 (oracle/lmi_oracle.py, a restatement of the reference's search) timed on this box's host
 cores on a bounded query sample.  ``--impl reference`` times only that CPU path.
+Extra keys: ``kernel_ms`` (per-stage CUDA-event means; ``scan_per_rank`` when N > 1),
+``host_enqueue_ms_per_step``, ``smallest_budget_with_recall_0.90`` (the metric's other reading: QPS
+at the smallest probed-bucket budget that still reaches recall 0.90; ``value`` stays on the README's
+budget of 4 buckets).
 
 Synthetic data: there is no network for the SISAP LAION files, so vectors are drawn from a
 768-d mixture (learnedmetricindex_b200/synthetic.py), L2-normalised, fp16; the index is a
