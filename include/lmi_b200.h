@@ -230,6 +230,13 @@ int lmi_merge_ranks(const double *dists_all, const uint32_t *nns_all, int64_t ra
 int lmi_merge_ranks_peer(const void *const *rank_base, int64_t nns_offset_bytes, int world, int nq,
                          int k, double *dists, uint32_t *nns, void *stream);
 
+/* All-gather by loads from peer memory (no collective library): dst[w*bytes_per_rank + i] =
+ * rank_base[w][i] for every rank w; rank_base as in lmi_merge_ranks_peer, bytes_per_rank a multiple
+ * of 16, dst 16-byte aligned.  Used for the query-sharded navigation's bucket order and for the
+ * query upload (each rank copies 1/world of the host batch over PCIe, the rest arrives over NVLink). */
+int lmi_gather_peer(const void *const *rank_base, int64_t bytes_per_rank, int world, void *dst,
+                    void *stream);
+
 #ifdef __cplusplus
 }
 #endif

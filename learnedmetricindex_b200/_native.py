@@ -81,6 +81,7 @@ _SIGNATURES = {
                                c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "lmi_merge_ranks": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p]),
+    "lmi_gather_peer": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "lmi_merge_ranks_peer": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
 }
 

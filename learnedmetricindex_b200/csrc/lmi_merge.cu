@@ -309,6 +309,17 @@ __global__ void merge_ranks_peer_kernel(const void* const* __restrict__ rank_bas
     }
 }
 
+// All-gather by loads from peer memory: dst[w * bytes + i] = rank_base[w][i] (16-byte words).
+__global__ void gather_peer_kernel(const void* const* __restrict__ rank_base, int64_t words_per_rank, int world,
+                                   uint4* __restrict__ dst) {
+    const int64_t total = words_per_rank * world;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int w = (int)(i / words_per_rank);
+        const int64_t j = i - (int64_t)w * words_per_rank;
+        dst[i] = static_cast<const uint4*>(rank_base[w])[j];
+    }
+}
+
 }  // namespace lmi
 
 extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, const int32_t* slot_of_pair,
@@ -362,5 +373,18 @@ extern "C" int lmi_merge_ranks_peer(const void* const* rank_base, int64_t nns_of
     if (smem > 48 * 1024) return LMI_E_UNSUPPORTED;
     lmi::merge_ranks_peer_kernel<<<(nq + warps - 1) / warps, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
         rank_base, nns_offset_bytes, world, nq, k, dists, nns);
+    return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lmi_gather_peer(const void* const* rank_base, int64_t bytes_per_rank, int world, void* dst,
+                               void* stream) {
+    if (!rank_base || !dst || world <= 0 || bytes_per_rank < 0) return LMI_E_BADARG;
+    if ((bytes_per_rank & 15) || (reinterpret_cast<uintptr_t>(dst) & 15)) return LMI_E_BADARG;
+    if (bytes_per_rank == 0) return 0;
+    const int64_t words = bytes_per_rank / 16;
+    int64_t blocks = (words * world + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    lmi::gather_peer_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        rank_base, words, world, static_cast<uint4*>(dst));
     return static_cast<int>(cudaGetLastError());
 }

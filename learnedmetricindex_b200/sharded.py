@@ -129,6 +129,41 @@ class PeerBuffers:
         return out_d, out_i
 
 
+class PeerGather:
+    """All-gather of one fixed-size block per rank by loads from peer memory (``lmi_gather_peer``):
+    the rank writes its block into a symmetric-memory buffer, a device-side barrier orders the
+    step, one kernel copies every peer's block over NVLink.  Two blocks alternate (see
+    ``PeerBuffers``)."""
+
+    def __init__(self, bytes_per_rank: int, world: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.bytes = -(-max(bytes_per_rank, 16) // 16) * 16
+        self.world = world
+        self.blocks, self.handles = [], []
+        for _ in range(2):
+            t = symm_mem.empty(self.bytes, dtype=torch.uint8, device=device)
+            t.zero_()
+            self.handles.append(symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD))
+            self.blocks.append(t)
+        self.turn = 0
+
+    def send_block(self) -> torch.Tensor:
+        return self.blocks[self.turn]
+
+    def gather(self) -> torch.Tensor:
+        """uint8[world * bytes]: every rank's block, in rank order (a fresh tensor)."""
+        from . import _native
+
+        hdl = self.handles[self.turn]
+        recv = torch.empty(self.world * self.bytes, dtype=torch.uint8, device=self.blocks[0].device)
+        hdl.barrier(channel=0)
+        _native.check(_native.lib().lmi_gather_peer(hdl.buffer_ptrs_dev, self.bytes, self.world, recv.data_ptr(),
+                                                    torch.cuda.current_stream().cuda_stream), "lmi_gather_peer")
+        self.turn ^= 1
+        return recv
+
+
 def merge_ranks_device(buf: GatherBuffers, out_d: torch.Tensor, out_i: torch.Tensor) -> None:
     """``lmi_merge_ranks`` over the gathered buffer (CUDA)."""
     from . import _native
@@ -213,12 +248,29 @@ class ShardedLearnedIndex:
                 events[0].record()
             start, stop, _ = query_slice(nq, self.world, self.rank)
             local_order, _ = self.local._bucket_order_device(qn[start:stop], int(n_buckets), list(n_categories))
-            order = gather_bucket_order(local_order, nq, int(n_buckets), self.group)
+            if isinstance(buf, PeerBuffers):
+                order = self._gather_rows_peer(local_order, nq)
+            else:
+                order = gather_bucket_order(local_order, nq, int(n_buckets), self.group)
         self.local.search_device(qn, qs, n_categories, n_buckets, k, events=events, out=buf.local_views(),
                                  bucket_order=order)
         if isinstance(buf, PeerBuffers):
             return buf.exchange_and_merge()
         return gather_and_merge(buf, self.group)
+
+    def _gather_rows_peer(self, part: torch.Tensor, n_rows: int) -> torch.Tensor:
+        """All-gather of row blocks over peer memory: ``part`` holds this rank's rows
+        ``query_slice(n_rows, world, rank)`` of a matrix; returns all ``n_rows`` rows."""
+        _, _, per = query_slice(n_rows, self.world, self.rank)
+        row_bytes = part.shape[1] * part.element_size()
+        key = ("rows", per, part.shape[1], part.dtype)
+        if key not in self._bufs:
+            self._bufs[key] = PeerGather(per * row_bytes, self.world, part.device, self.group)
+        pg = self._bufs[key]
+        blk = pg.send_block()[: per * row_bytes].view(part.dtype).view(per, part.shape[1])
+        blk[: part.shape[0]] = part
+        full = pg.gather().view(self.world, pg.bytes)[:, : per * row_bytes].reshape(-1)
+        return full.view(part.dtype).view(self.world * per, part.shape[1])[:n_rows].contiguous()
 
     def _upload_sharded(self, host_matrix, dev) -> torch.Tensor:
         """Host queries -> device on every rank: each rank copies only its 1/world slice over PCIe and
@@ -230,6 +282,8 @@ class ShardedLearnedIndex:
             return to_device_matrix(host_matrix, dev)
         start, stop, per = query_slice(nq, self.world, self.rank)
         part = to_device_matrix(host_matrix[start:stop], dev)
+        if self.exchange == "peer" and torch.device(dev).type == "cuda":
+            return self._gather_rows_peer(part, nq)
         send = torch.zeros((per, part.shape[1]), dtype=part.dtype, device=dev)
         send[: stop - start] = part
         recv = torch.empty((self.world * per, part.shape[1]), dtype=part.dtype, device=dev)

@@ -43,6 +43,16 @@ def main():
             # host-facing API (queries uploaded 1/world per rank and all-gathered)
             dh, ih, _ = eng.search(None, Q.cpu().numpy(), None, Q.cpu().numpy(), None, [C], n_buckets=B, k=k)
             assert np.array_equal(dh, exp_d.cpu().numpy()) and np.array_equal(ih.view(np.int32), exp_i.cpu().numpy())
+    # a batch that does not divide by the number of ranks (padded navigation / upload slices)
+    for exchange in ("peer", "nccl"):
+        li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+        li.attach_layout(full.restrict_to_buckets(parts[rank]))
+        eng = ShardedLearnedIndex(li, exchange=exchange)
+        Qodd = Q[:999].contiguous()
+        exp_d, exp_i = ref.search_device(Qodd, Qodd, [C], 3, 10)
+        for rep in range(2):
+            dh, ih, _ = eng.search(None, Qodd.cpu().numpy(), None, Qodd.cpu().numpy(), None, [C], n_buckets=3, k=10)
+            assert np.array_equal(dh, exp_d.cpu().numpy()) and np.array_equal(ih.view(np.int32), exp_i.cpu().numpy())
     # equal row slices of every bucket: same result for k <= 10 (distances always; ids on real candidates)
     li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
     li.attach_layout(full.restrict_to_slice(rank, world))
