@@ -94,6 +94,18 @@ class LearnedIndex:
         """From a (possibly unpickled) reference ``LearnedIndex`` (:23-39)."""
         return cls(li.root_model, getattr(li, "internal_models", {}), getattr(li, "bucket_paths", []), **kw)
 
+    # ------------------------------------------------------------------ pickling ----
+    def __getstate__(self):
+        """``save_as_pickle(filename, li)`` (search/li/utils.py:14-29, search/search.py:226-235) keeps the
+        models and bucket paths; the device layout, like ``data_prediction`` in the reference
+        (search.py:228), is not part of the pickle and is rebuilt by the first ``search``."""
+        return {"root_model": self.root_model, "internal_models": self.internal_models,
+                "bucket_paths": self.bucket_paths, "scan_impl": self.scan_impl}
+
+    def __setstate__(self, state):
+        self.__init__(state["root_model"], state["internal_models"], state["bucket_paths"],
+                      scan_impl=state.get("scan_impl", 0))
+
     # ------------------------------------------------------------------ layout ------
     def attach_layout(self, layout: DeviceBucketLayout) -> None:
         """Use a device layout built elsewhere (e.g. data generated on the GPU)."""

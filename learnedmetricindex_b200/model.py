@@ -92,6 +92,15 @@ class NeuralNetwork:
         layers = [(sd[f"{prefix}{i}.weight"], sd[f"{prefix}{i}.bias"]) for i in idx]
         return cls(layers, device=device)
 
+    # -- pickling (search/li/utils.py:14-29 saves the whole index with pickle) -----------
+    def __getstate__(self):
+        return {"layers": [(W.cpu().numpy(), b.cpu().numpy()) for W, b in self.layers], "model_type": self.model_type,
+                "impl": self.impl}
+
+    def __setstate__(self, state):
+        self.__init__(state["layers"], state.get("model_type"))
+        self.impl = state.get("impl", self.impl)
+
     # -- kernels ----------------------------------------------------------------------
     def _split(self, t: torch.Tensor, exact_in_one_part: bool):
         """hi/mid/lo tf32 parts of a device tensor (``lmi_split_tf32``)."""

@@ -528,3 +528,25 @@ def test_full_size_properties_10m():
     assert 0.85 < r4 <= 1.0
     # returned ids are real rows and their distances re-compute from the stored vectors
     np.testing.assert_allclose(d4, distances_of(i4), rtol=1e-3, atol=2e-6)
+
+
+def test_pickle_roundtrip_like_save_as_pickle(tmp_path):
+    """search/li/utils.py:14-29: the driver pickles the index after the build and searches with the
+    loaded one; weights, internal models and bucket paths survive, the layout is rebuilt."""
+    import pickle
+
+    c = MultiLevelCase("ml_4x3")
+    from learnedmetricindex_b200 import LearnedIndex
+
+    li = LearnedIndex(c.root_layers, c.internal, c.bucket_paths)
+    d0, i0, _ = li.search(None, c.Q, c.X, c.Q, c.data_prediction, c.n_categories, n_buckets=3, k=10)
+    path = tmp_path / "li.pkl"
+    with open(path, "wb") as f:
+        pickle.dump(li, f)
+    with open(path, "rb") as f:
+        li2 = pickle.load(f)
+    assert li2.bucket_paths == li.bucket_paths and set(li2.internal_models) == set(li.internal_models)
+    assert li2._layout is None
+    d1, i1, _ = li2.search(None, c.Q, c.X, c.Q, c.data_prediction, c.n_categories, n_buckets=3, k=10)
+    np.testing.assert_array_equal(d0, d1)
+    np.testing.assert_array_equal(i0, i1)
