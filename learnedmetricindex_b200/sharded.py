@@ -226,6 +226,21 @@ class ShardedLearnedIndex:
         # "nccl": all-gather + lmi_merge_ranks (GatherBuffers; also what the gloo tests run)
         self.exchange = exchange or os.environ.get("LMI_EXCHANGE", "peer")
         self._bufs = {}
+        if self.exchange == "peer" and self.world > 1 and torch.device(local.device).type == "cuda":
+            # symmetric memory needs P2P mappings between all GPUs of the group: probe once and let every
+            # rank agree on the outcome (a rank that cannot map its peers must not leave the others waiting)
+            ok = 1
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+
+                t = symm_mem.empty(16, dtype=torch.uint8, device=local.device)
+                symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD)
+            except Exception:  # noqa: BLE001 -- any failure means "use the collective library"
+                ok = 0
+            flag = torch.tensor([ok], dtype=torch.int32, device=local.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if int(flag.item()) == 0:
+                self.exchange = "nccl"
 
     def _buffers(self, nq: int, k: int, device):
         key = (nq, k)
