@@ -48,6 +48,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is a CPU measurement on ALL host
+# cores (rank 0 alone works there), so that default must not leak into it
+if "--impl" in sys.argv and "reference" in sys.argv and os.environ.get("OMP_NUM_THREADS") == "1":
+    del os.environ["OMP_NUM_THREADS"]
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -276,8 +281,8 @@ def build_workload(args, device, rank, world, use_repo_kernels=True):
             xs = x if sel.numel() == m else x[sel].contiguous()
             if use_repo_kernels:
                 _native.check(L.lmi_scatter_rows(xs.data_ptr(), 1, dsel.data_ptr(), int(sel.numel()), D,
-                                                 vectors.data_ptr(), D, torch.cuda.current_stream().cuda_stream),
-                              "lmi_scatter_rows")
+                                                 vectors.data_ptr(), D, None,
+                                                 torch.cuda.current_stream().cuda_stream), "lmi_scatter_rows")
                 torch.cuda.current_stream().synchronize()
             else:
                 vectors[dsel] = xs
@@ -333,7 +338,7 @@ def recall_at_10(nns, gt):
 
 
 # --------------------------------------------------------------------------------------
-# CPU baseline (oracle port), bounded sample
+# CPU side: the oracle port and the unmodified reference, on the WHOLE query batch
 # --------------------------------------------------------------------------------------
 def host_threads():
     try:
@@ -342,8 +347,19 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def use_all_host_threads():
+    """All cores of this process' affinity mask, whatever OMP_NUM_THREADS the launcher exported."""
+    n = host_threads()
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 class CpuBaseline:
-    """The oracle (CPU restatement of LearnedIndex.search) over the same index, host side."""
+    """The CPU implementations of the path over the same index, host side:
+    ``run``            the oracle port (oracle/lmi_oracle.py: the reference's arithmetic without its per-round
+                       groupby / .loc copies) -- the FASTER of the two, so the one the ratio is quoted against;
+    ``run_unmodified`` the reference's own ``LearnedIndex.search`` (search/li/LearnedIndex.py:41-161), staged
+                       byte-identical under oracle/_ref (oracle/build_ref.py), through oracle/ref_harness.py."""
 
     def __init__(self, w, C):
         import psutil
@@ -355,7 +371,8 @@ class CpuBaseline:
         self.C = C
         self.layers = syn.layers_to_numpy(w["layers"])
         vec = w["vectors"].cpu().numpy()
-        ids = (w["ids"].cpu().numpy().view(np.uint32)).astype(np.int64)
+        self.ids = (w["ids"].cpu().numpy().view(np.uint32)).astype(np.int64)
+        self.offsets = np.asarray(w["bucket_off"], dtype=np.int64)
         need_f32 = vec.size * 4
         avail = psutil.virtual_memory().available
         self.f32 = avail > 2.5 * need_f32 + (8 << 30)
@@ -363,32 +380,124 @@ class CpuBaseline:
             # the reference's frames are f32 after data_X_to_torch / faiss' cast; pre-widening once is
             # generous to the CPU side (the reference re-copies every bucket every round, :357)
             vec = torch.from_numpy(vec).float().numpy()
-        self.layout = orc.BucketMajor.from_grouped(vec, w["bucket_off"], ids)
+        self.layout = orc.BucketMajor.from_grouped(vec, self.offsets, self.ids)
         self.Q = w["Q"].cpu().numpy()
         self.index = orc.OracleIndex(self.layers)
-        self.threads = torch.get_num_threads()
+        self.threads = use_all_host_threads()
+        self.ram_gb = psutil.virtual_memory().total / 2 ** 30
 
-    def run(self, n_queries, B):
-        q = self.Q[:n_queries]
+    def run(self, B, n_queries=None):
+        q = self.Q if n_queries is None else self.Q[:n_queries]
         t0 = time.perf_counter()
         d, i, times, order = self.orc.search(self.index, q, None, q, None, [self.C], n_buckets=B, k=K_NN,
                                              layout=self.layout)
-        return time.perf_counter() - t0, d, i
+        return time.perf_counter() - t0, d, i, order
 
-    def describe(self, n_queries, B, nq_total):
-        return (f"first {n_queries} of the {nq_total} queries against the full index, B={B}, oracle/lmi_oracle.py "
+    def run_single_thread(self, B, n_queries=None):
+        """The port on ONE thread -- the figure that sits beside the README's 1-core 45 QPS (README.md:54-68)."""
+        n = torch.get_num_threads()
+        torch.set_num_threads(1)
+        try:
+            return self.run(B, n_queries)
+        finally:
+            torch.set_num_threads(n)
+
+    def unmodified_available(self):
+        from oracle import ref_harness
+
+        return ref_harness.reference_available()
+
+    def run_unmodified(self, B, limit_s=600.0):
+        """ONE call of the reference's own ``LearnedIndex.search`` on the whole batch.  The two DataFrames
+        view this object's f32 matrix (rows are bucket-major there; ``data_prediction`` and the index labels
+        are permuted alike, so the groupby yields the same groups in the same order as on the original
+        frame).  Returns (seconds, dists, nns, measured_time) or raises (RAM guard / time limit)."""
+        import signal
+
+        import psutil
+
+        from oracle import ref_harness
+
+        vec = self.layout.vectors
+        if vec.dtype != np.float32:
+            raise MemoryError("vectors were not widened to f32 (host RAM too small for the reference's frames)")
+        # the reference holds the frame, one regrouped copy of it per round and the bucket being scanned
+        need = 1.35 * vec.nbytes + (6 << 30)
+        if psutil.virtual_memory().available < need:
+            raise MemoryError(f"reference search needs ~{need / 2 ** 30:.0f} GiB free, "
+                              f"{psutil.virtual_memory().available / 2 ** 30:.0f} GiB available")
+        li = ref_harness.make_reference_index(self.layers, "MLP-4")  # MLP pinned to the CPU (model.py:124-125)
+        labels = np.repeat(np.arange(self.C, dtype=np.int64), np.diff(self.offsets)).reshape(-1, 1)
+
+        def on_alarm(signum, frame):
+            raise TimeoutError(f"reference search exceeded {limit_s:.0f} s")
+
+        old = signal.signal(signal.SIGALRM, on_alarm)
+        signal.alarm(int(limit_s))
+        try:
+            t0 = time.perf_counter()
+            d, i, tm = ref_harness.run_reference_search(li, vec, self.Q, vec, self.Q, labels, [self.C], B, K_NN,
+                                                        ids=self.ids, copy=False)
+            dt = time.perf_counter() - t0
+        finally:
+            signal.alarm(0)
+            signal.signal(signal.SIGALRM, old)
+        return dt, d, i, tm
+
+    def describe(self, B, nq):
+        return (f"all {nq} of the {nq} queries against the full index, B={B}, oracle/lmi_oracle.py "
                 f"(torch CPU MLP + per-bucket f32 sgemm + top-10 + stable merge), vectors "
                 f"{'pre-widened to f32 once' if self.f32 else 'fp16, widened per bucket per round'}, "
                 f"{self.threads} torch threads")
 
-
-def pick_sample(t_probe, n_probe, nq, budget_s, runs):
-    per_q = t_probe / max(1, n_probe)
-    s = int(budget_s / max(1e-9, per_q * runs))
-    s = max(min(n_probe, nq), min(nq, s))
-    if s >= 1000:
-        s = s // 500 * 500
-    return min(nq, s)
+    # -- parity of a GPU result against this CPU result ----------------------------------------------
+    def explain(self, d_cpu, i_cpu, order_cpu, d_gpu, i_gpu, order_gpu, tie_abs=4e-6, prob_tie=1e-6):
+        """Every difference between the GPU result and the oracle's must be a tie the north_star tolerates:
+        a bucket-order row may differ only where the swapped classes' probabilities are within 1e-6;
+        on rows with the same bucket order an id may differ only where the object the GPU returned is, by an
+        exact float64 inner product on the host vectors, within ``tie_abs`` of the oracle's entry at that
+        position (two objects at the same distance up to f32 rounding).  Returns the parity dict."""
+        nq, k = i_cpu.shape
+        order_cpu = order_cpu[:, :, 0]
+        rows_equal = (order_gpu == order_cpu).all(axis=1)
+        unexplained_order = 0
+        bad_rows = np.flatnonzero(~rows_equal)
+        if bad_rows.size:
+            probs, classes = self.orc.predict_proba(self.layers, self.orc.to_f32_tensor(self.Q[bad_rows]))
+            for j, q in enumerate(bad_rows):
+                p_of = np.empty(self.C, dtype=np.float64)
+                p_of[classes[j]] = probs[j]
+                diff = order_gpu[q] != order_cpu[q]
+                if np.abs(p_of[order_gpu[q][diff]] - p_of[order_cpu[q][diff]]).max() > prob_tie:
+                    unexplained_order += 1
+        ok = rows_equal
+        mism = (i_gpu != i_cpu) & ok[:, None]
+        rel = np.abs(d_gpu - d_cpu) / np.maximum(np.abs(d_cpu), 1e-3)
+        finite = np.isfinite(d_cpu) & (np.abs(d_cpu) < 1e38)
+        dist_bad = int(((rel > 1e-3) & finite & ok[:, None] & ~mism).sum())
+        unexplained = 0
+        qs, js = np.nonzero(mism)
+        row_of_id = None
+        if qs.size:
+            sorter = np.argsort(self.layout.ids, kind="stable")
+            for q, j in zip(qs.tolist(), js.tolist()):
+                gid = int(i_gpu[q, j])
+                pos = np.searchsorted(self.layout.ids, gid, sorter=sorter)
+                if pos >= sorter.size or self.layout.ids[sorter[pos]] != gid:
+                    unexplained += 1
+                    continue
+                x = self.layout.vectors[sorter[pos]].astype(np.float64)
+                true_d = 1.0 - float(np.dot(x, self.Q[q].astype(np.float64)))
+                if abs(true_d - float(d_cpu[q, j])) > tie_abs:
+                    unexplained += 1
+        n_ok = int(ok.sum())
+        return {"bucket_order_rows_equal": float(rows_equal.mean()),
+                "bucket_order_rows_unexplained": int(unexplained_order),
+                "id_agreement": float((i_gpu[ok] == i_cpu[ok]).mean()) if n_ok else None,
+                "id_mismatches": int(mism.sum()), "unexplained": int(unexplained + unexplained_order + dist_bad),
+                "dists_beyond_rel_1e-3": dist_bad, "queries": int(nq),
+                "rule": f"ids equal except where the exact f64 distance of the returned object is within {tie_abs:g} "
+                        f"of the oracle's entry (f32 rounding tie); bucket rows equal except probability ties <= {prob_tie:g}"}
 
 
 # --------------------------------------------------------------------------------------
@@ -544,6 +653,12 @@ def main():
     ap.add_argument("--latent", type=int, default=24)
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reference-extras", action="store_true",
+                    help="--impl reference: skip the 1-thread call and the unmodified-reference call")
+    ap.add_argument("--reference-limit", type=float, default=600.0,
+                    help="time limit (s) of the ONE unmodified li.LearnedIndex.search call")
+    ap.add_argument("--no-workload-c", action="store_true",
+                    help="skip the appended 100M x 768 measurement (BASELINE.json configs[2])")
     ap.add_argument("--sweep", default="", help="comma list of B values: print recall/QPS per B to stderr")
     ap.add_argument("--balance", default="size2", choices=["calibrated", "size2"],
                     help="--shard buckets: LPT cost = rows^2 (queries follow the data; measured the more robust of the "
@@ -556,18 +671,14 @@ def main():
     ap.add_argument("--ml-model-type", default="MLP", help="--workload ml: model type of every tree node")
     ap.add_argument("--ml-cpu-queries", type=int, default=2000, help="--workload ml: queries of the cpu_baseline leg")
     args = ap.parse_args()
-    if args.shard == "auto":
-        w_ = int(os.environ.get("WORLD_SIZE", "1"))
-        n_ = args.n or WORKLOADS[args.workload]["n"]
-        c_ = args.buckets or WORKLOADS[args.workload]["buckets"]
-        args.shard = "rows" if w_ > 1 and n_ // (w_ * c_) >= 4 * 16384 else "buckets"
+    args.default_sizes = not (args.n or args.nq or args.buckets)  # before the workload defaults are filled in
     if args.probe is None:
         args.probe = 10 if args.workload == "ml" else 4
     wl = WORKLOADS[args.workload]
     args.n = args.n or wl["n"]
     args.nq = args.nq or wl["nq"]
     args.buckets = args.buckets or wl["buckets"]
-    wl_name = wl["name"] if (args.n, args.nq, args.buckets) == (wl["n"], wl["nq"], wl["buckets"]) else \
+    wl_name = wl["name"] if args.default_sizes else \
         f"{args.n} x 768 fp16, {args.buckets} buckets, MLP-4, {args.nq} queries, k=10"
     assert args.warmup >= 0 and args.steps >= 1
 
@@ -589,12 +700,69 @@ def main():
         dist.init_process_group("nccl", device_id=device)
     assert world == args.gpus or world == 1 and args.gpus == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
+    out = measure(args, wl_name, device, rank, world, local_rank, headline=True)
+
+    # BASELINE.json configs[2] (north_star: ">= 6x scaling from 1 to 8 GPUs on 100M x 768") rides on the same
+    # line at every N -- one B200 holds the 153.6 GB index, so the 1-GPU point exists -- as "workload_c"
+    if args.workload == "b" and args.default_sizes and not args.no_workload_c:
+        import copy
+        import gc
+
+        gc.collect()
+        torch.cuda.empty_cache()
+        ac = copy.copy(args)
+        ac.workload, ac.n, ac.shard = "c", WORKLOADS["c"]["n"], "auto"
+        ac.steps, ac.warmup = min(args.steps, 10), 3
+        try:
+            oc = measure(ac, WORKLOADS["c"]["name"], device, rank, world, local_rank, headline=False)
+            keep = ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "e2e",
+                    "kernel_ms", "roofline", "clocks", "gpu_launches", "host_enqueue_ms_per_step", "multi_gpu_parity")
+            out["workload_c"] = {k_: oc[k_] for k_ in keep if k_ in oc}
+        except Exception as e:  # noqa: BLE001 -- the headline stands; say why the 100M point is absent
+            log(f"workload c failed: {e!r}")
+            out["workload_c"] = {"error": repr(e)}
+    if rank == 0:
+        emit_json(out)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def all_ranks_ok(ok, device, world):
+    """True only when every rank reports success (a rank that failed must not leave the others in a collective)."""
+    if world == 1:
+        return bool(ok)
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item())
+
+
+def result_checksum(d, i):
+    """Order-sensitive 64-bit checksum of a device result (dists f64[nq,k], nns i32[nq,k])."""
+    w = torch.arange(1, d.numel() + 1, dtype=torch.int64, device=d.device)
+    a = (d.reshape(-1).view(torch.int64) * w).sum()
+    b = (i.reshape(-1).to(torch.int64) * (w + 7)).sum()
+    return int((a ^ (b << 1)).item())
+
+
+def measure(args, wl_name, device, rank, world, local_rank, headline):
+    """Build the workload ``args`` describes over the ``world`` ranks, check it, time it; returns the JSON object.
+    ``headline=False`` (the appended 100M point) skips the CPU leg, the budget search and the sweeps."""
+    if args.shard == "auto":
+        args.shard = "rows" if world > 1 and args.n // (world * args.buckets) >= 4 * 16384 else "buckets"
+
     from learnedmetricindex_b200 import DeviceBucketLayout, LearnedIndex, _native
     from learnedmetricindex_b200.sharded import ShardedLearnedIndex
 
     _native.lib()  # fail loudly if the CUDA library is missing
     C, nq = args.buckets, args.nq
-    w = build_workload(args, device, rank, world)
+    w, err = None, None
+    try:
+        w = build_workload(args, device, rank, world)
+    except Exception as e:  # noqa: BLE001 (e.g. out of memory on one rank)
+        err = e
+    if not all_ranks_ok(err is None, device, world):
+        raise RuntimeError(f"workload construction failed on some rank: {err!r}")
     layout = DeviceBucketLayout(w["vectors"], torch.from_numpy(w["bucket_off"]), w["ids"])
     li = LearnedIndex(w["layers"], {}, [(i,) for i in range(C)])
     li.attach_layout(layout)
@@ -605,8 +773,8 @@ def main():
     gt = ground_truth(Q, w["vectors"], w["ids"], world)
     log(f"ground truth (exact top-10 over {args.n} rows) {time.time() - t0:.1f}s")
 
-    def run_once(B):
-        d, i = engine.search_device(Q, Q, [C], B, K_NN)
+    def run_once(B, eng=None):
+        d, i = (eng or engine).search_device(Q, Q, [C], B, K_NN)
         torch.cuda.synchronize()
         return d.cpu().numpy(), i.cpu().numpy().view(np.uint32)
 
@@ -631,23 +799,70 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    host_enqueue_ms = [0.0]
+    # ---- multi-GPU parity, asserted before anything is timed ----
+    multi = None
+    if world > 1:
+        d_p, i_p = engine.search_device(Q, Q, [C], B, K_NN)
+        d_p, i_p = d_p.clone(), i_p.clone()
+        # (1) the two exchange paths (peer-memory merge kernel / NCCL all-gather + merge) are bit-identical
+        eng_nccl = ShardedLearnedIndex(li, exchange="nccl")
+        d_n, i_n = eng_nccl.search_device(Q, Q, [C], B, K_NN)
+        modes_equal = bool(torch.equal(d_p, d_n) and torch.equal(i_p, i_n))
+        # (2) every rank holds the same final [nq, k]
+        cs = torch.tensor([result_checksum(d_p, i_p)], dtype=torch.int64, device=device)
+        all_cs = [torch.empty_like(cs) for _ in range(world)]
+        dist.all_gather(all_cs, cs)
+        same_everywhere = len({int(c.item()) for c in all_cs}) == 1
+        multi = {"exchange": engine.exchange, "exchange_modes_bit_equal": modes_equal,
+                 "ranks_hold_same_result": same_everywhere}
+        # (3) sharded == unsharded: rank 0 rebuilds the WHOLE index on its own GPU (fits at 10M) and searches it
+        if args.n * D * 2 <= 40e9:
+            same_unsharded = True
+            if rank == 0:
+                w1 = build_workload(args, device, 0, 1)
+                li1 = LearnedIndex(w1["layers"], {}, [(i,) for i in range(C)])
+                li1.attach_layout(DeviceBucketLayout(w1["vectors"], torch.from_numpy(w1["bucket_off"]), w1["ids"]))
+                d_1, i_1 = li1.search_device(Q, Q, [C], B, K_NN)
+                torch.cuda.synchronize()
+                same_unsharded = bool(torch.equal(d_1, d_p) and torch.equal(i_1, i_p))
+                del w1, li1, d_1, i_1
+                torch.cuda.empty_cache()
+            flag = torch.tensor([1 if same_unsharded else 0], dtype=torch.int32, device=device)
+            dist.broadcast(flag, 0)
+            multi["sharded_equals_unsharded"] = bool(flag.item())
+        del eng_nccl
+        log(f"multi-GPU parity: {multi}")
+        assert modes_equal, "peer-memory and NCCL exchange paths disagree"
+        assert same_everywhere, "ranks hold different final results"
+        assert multi.get("sharded_equals_unsharded", True), "sharded result differs from the unsharded search"
 
-    def timed_device_loop(Bp, steps, warmup, collect_scan=True):
+    host_enqueue_ms = [0.0]
+    can_graph = world == 1 or getattr(engine, "exchange", "") == "peer"
+
+    def timed_device_loop(Bp, steps, warmup, graph=False):
+        """``steps`` back-to-back searches with device-resident queries, CUDA events around the region.
+        graph=False: eager launches with an event between the stages of every step (the per-kernel split
+        and the scan's launch duration come from here); graph=True: the product's default path, one CUDA
+        graph replay per search (its stage events are graph nodes, read for the last step only)."""
+        graph = graph and can_graph
         evs = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(steps)]
+        step = (lambda ev: engine.search_graphed(Q, Q, [C], Bp, K_NN)) if graph else \
+            (lambda ev: engine.search_device(Q, Q, [C], Bp, K_NN, events=ev))
         for _ in range(warmup):
-            engine.search_device(Q, Q, [C], Bp, K_NN)
+            step(None)
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_a = time.time()
         e0.record()
         for s in range(steps):
-            engine.search_device(Q, Q, [C], Bp, K_NN, events=evs[s])
+            res = step(evs[s])
         e1.record()
-        host_enqueue_ms[0] = (time.time() - t_a) * 1e3 / steps  # host time to enqueue one step's launches
+        host_enqueue_ms[0] = (time.time() - t_a) * 1e3 / steps  # host time to enqueue one step
         barrier()
         t_b = time.time()
         total_ms = e0.elapsed_time(e1)
+        if graph:
+            evs = [res[2]]
         scan_ms = [ev[2].elapsed_time(ev[3]) for ev in evs]
         parts = {name: float(np.mean([ev[a].elapsed_time(ev[b]) for ev in evs]))
                  for name, a, b in (("mlp_topn", 0, 1), ("invert", 1, 2), ("scan", 2, 3), ("merge", 3, 4))}
@@ -661,19 +876,23 @@ def main():
             parts["scan_per_rank"] = [round(v, 4) for v in per_rank.tolist()]
         return total_ms, scan_ms, parts, (t_a, t_b)
 
-    if args.sweep:
+    if args.sweep and headline:
         for Bs in [int(v) for v in args.sweep.split(",")]:
             r = recall_at_10(run_once(Bs)[1], gt)
-            tm, sc, parts, _ = timed_device_loop(Bs, 10, 3)
-            log(f"sweep B={Bs}: recall@10={r:.4f} QPS={nq / (tm / 10 / 1e3):.0f} ms/step={tm / 10:.3f} parts={parts}")
+            tm, sc, parts_s, _ = timed_device_loop(Bs, 10, 3)
+            log(f"sweep B={Bs}: recall@10={r:.4f} QPS={nq / (tm / 10 / 1e3):.0f} ms/step={tm / 10:.3f} parts={parts_s}")
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     K, W = args.steps, max(args.warmup, 3)
-    total_ms, scan_ms, parts, win_dev = timed_device_loop(B, K, W)
+    # the timed region: K graph replays (what `search` does per call); then the same K steps as eager
+    # launches with events between the stages, for the per-kernel split and the scan's launch duration
+    total_ms, _, parts_graph, win_dev = timed_device_loop(B, K, W, graph=True)
     ms_per_step = total_ms / K
     value = nq / (ms_per_step / 1e3)
     host_ms_main = host_enqueue_ms[0]
+    total_ms_eager, scan_ms, parts, win_eager = timed_device_loop(B, K, W, graph=False)
+    host_ms_eager = host_enqueue_ms[0]
 
     # ---- end to end: host queries (pinned) -> search() -> host results, every step ----
     Qh = torch.empty(Q.shape, dtype=Q.dtype).pin_memory()
@@ -697,6 +916,7 @@ def main():
     h2d = Qh.numel() * Qh.element_size()
     d2h = d_e2e.nbytes + i_e2e.nbytes
     assert recall_at_10(i_e2e, gt) >= recall - 1e-9
+    order_gpu = li.last_bucket_order.cpu().numpy() if li.last_bucket_order is not None else None
 
     # ---- roofline of the scan kernel (this rank's launch) ----
     peaks = {}
@@ -705,11 +925,10 @@ def main():
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    clocks = sampler.summary([win_dev, (t_a, t_b)])
-    # burst peak for a kernel timed alone, sustained for one timed inside a long step: the timed region
-    # is K back-to-back steps (the scan is ~90 % of each), so it counts as "long" when it lasts >= 1 s or
-    # the clock samples taken during it show the power cap engaged (cuBLAS at the burst figure does not)
-    long_region = total_ms >= 1000.0 or "sw_power_cap" in clocks.get("reasons", [])
+    clocks = sampler.summary([win_dev, win_eager, (t_a, t_b)])
+    # burst peak (cuBLAS timed alone) unless the timed region itself lasts >= 1 s; the sustained figure
+    # (cuBLAS looping under the power cap) rides along as a note
+    long_region = total_ms_eager >= 1000.0
     tf_burst = float(peaks.get("bf16_tflops", 1590.0))
     tf_sustained = float(peaks.get("bf16_tflops_sustained", 1400.0))
     tf_peak = tf_sustained if long_region else tf_burst
@@ -722,7 +941,7 @@ def main():
     t_tensor, t_hbm = flops / (tf_peak * 1e12), bytes_alg / (hbm_peak * 1e9)
     traffic = None
     try:  # ncu dram bytes of one launch: only valid for the exact single-GPU default configuration it was taken on
-        if world == 1 and not (args.n or args.nq or args.buckets) and args.probe == 4:
+        if world == 1 and args.default_sizes and B == 4:
             traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get(args.workload)
     except Exception:
         pass
@@ -738,26 +957,24 @@ def main():
     roof.update(kernel="scan_topk_tc_kernel", launch_ms=scan_s * 1e3, alg_flops=flops, alg_bytes=bytes_alg,
                 hbm_gbs_achieved=bytes_alg / scan_s / 1e9, tflops_achieved=flops / scan_s / 1e12,
                 peak_source=("MEASURED_PEAKS.json" if peaks else "fallback") +
-                            (" (sustained: back-to-back steps, power cap engaged or >= 1 s)" if long_region and peaks
-                             else " (burst)" if peaks else ""))
+                            (" (sustained: the timed region lasts >= 1 s)" if long_region else " (burst)"),
+                traffic_source="profiles/scan_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one "
+                               "launch (ncu --set full)" if traffic is not None else None)
 
-    # ---- CPU baseline (rank 0, N == 1 only) ----
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    # ---- CPU baseline (rank 0, N == 1 only): the oracle port on the WHOLE batch, which doubles as the
+    # asserted parity check of the timed GPU result at the headline size ----
+    cpu = parity = None
+    if headline and rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             t0 = time.time()
             cb = CpuBaseline(w, C)
-            n_probe = min(nq, 200)
-            t_probe, _, _ = cb.run(n_probe, B)
-            S = pick_sample(t_probe, n_probe, nq, args.cpu_budget, 1)
-            t_cpu, d_cpu, i_cpu = cb.run(S, B)
-            # the sample doubles as a parity check of the timed GPU result
-            agree = float((i_cpu == i_e2e[:S]).mean())
-            cpu = {"value": S / t_cpu, "unit": "QPS", "cores": cb.threads, "kind": "port",
-                   "sample": cb.describe(S, B, nq), "seconds": t_cpu, "host_cpus": host_threads(),
-                   "id_agreement_with_gpu": agree}
-            log(f"cpu baseline: {S} queries in {t_cpu:.2f}s = {S / t_cpu:.1f} QPS on {cb.threads} threads "
-                f"(setup {time.time() - t0 - t_cpu:.1f}s); id agreement with the GPU result {agree:.5f}")
+            t_cpu, d_cpu, i_cpu, order_cpu = cb.run(B)
+            parity = cb.explain(d_cpu, i_cpu, order_cpu, d_e2e, i_e2e, order_gpu)
+            cpu = {"value": nq / t_cpu, "unit": "QPS", "cores": cb.threads, "kind": "port",
+                   "sample": cb.describe(B, nq), "seconds": t_cpu, "host_cpus": host_threads(),
+                   "id_agreement_with_gpu": parity["id_agreement"]}
+            log(f"cpu baseline: {nq} queries in {t_cpu:.2f}s = {nq / t_cpu:.1f} QPS on {cb.threads} threads "
+                f"(setup {time.time() - t0 - t_cpu:.1f}s); parity {parity}")
             del cb
         except Exception as e:  # the GPU numbers stand; say why the CPU leg is absent
             cpu = {"value": None, "unit": "QPS", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
@@ -765,19 +982,19 @@ def main():
     # ---- the metric's other reading: the SMALLEST budget whose recall@10 is still >= 0.90;
     # the headline `value` stays on the README's budget (`--probe`, 4 of 120 buckets) ----
     min_point = None
-    Bm, rm = B, recall
-    while Bm > 1:
-        r = recall_at_10(run_once(Bm - 1)[1], gt)
-        if r < 0.90:
-            break
-        Bm, rm = Bm - 1, r
-    if Bm < B:
-        ks = min(K, 10)
-        tm, _, _, _ = timed_device_loop(Bm, ks, 3)
-        min_point = {"probed_buckets": Bm, "recall_at_10": rm, "qps": nq / (tm / ks / 1e3), "ms_per_step": tm / ks}
+    if headline:
+        Bm, rm = B, recall
+        while Bm > 1:
+            r = recall_at_10(run_once(Bm - 1)[1], gt)
+            if r < 0.90:
+                break
+            Bm, rm = Bm - 1, r
+        if Bm < B:
+            ks = min(K, 10)
+            tm, _, _, _ = timed_device_loop(Bm, ks, 3, graph=True)
+            min_point = {"probed_buckets": Bm, "recall_at_10": rm, "qps": nq / (tm / ks / 1e3), "ms_per_step": tm / ks}
 
-    # split_tf32 (queries), linear_tc x2, softmax_topn, invert x3, scan, merge(, rank merge)
-    launches_per_step = 1 + 2 + 1 + 3 + 1 + 1 + (1 if world > 1 else 0)
+    launches_per_step = getattr(li, "launches_per_search", 9) + (1 if world > 1 else 0)
     out = {
         "metric": "QPS at recall@10>=0.90", "value": value, "unit": "QPS", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -792,22 +1009,32 @@ def main():
                 "ms_per_step": e2e_s / K * 1e3},
         "gpu_launches": launches_per_step * K,
         "host_enqueue_ms_per_step": host_ms_main,
+        "execution": ("one CUDA graph replay per search" if can_graph else "eager launches (NCCL exchange)"),
+        "eager_launches": {"ms_per_step": total_ms_eager / K, "host_enqueue_ms_per_step": host_ms_eager},
         "kernel_ms": parts,
+        "kernel_ms_graph_last_step": parts_graph if can_graph else None,
         "roofline": roof,
         "cpu_baseline": cpu,
+        "parity": parity,
+        "multi_gpu_parity": multi,
         "clocks": clocks,
         "smallest_budget_with_recall_0.90": min_point,
     }
-    if rank == 0:
-        emit_json(out)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    if parity is not None and parity["unexplained"] > 0:
+        # a fast kernel whose results differ from the reference's is not done: print the line, then fail
+        if rank == 0:
+            emit_json(out)
+        raise SystemExit(f"parity with the CPU oracle FAILED at the headline size: {parity}")
+    return out
 
 
 def run_reference(args, wl_name, rank, world, local_rank):
-    """The reference's CPU search (oracle port: the reference is pure Python over faiss/pandas
-    and /root/reference does not exist on the GPU box) on this box's host cores."""
+    """The reference arm: the CPU implementation of the path on this box's host cores, on the SAME config
+    (all ``nq`` queries per step, all host threads).  ``value`` is the oracle port -- the reference's
+    arithmetic without its per-round pandas regrouping, i.e. the faster of the two CPU forms, so the
+    GPU/CPU ratio is the conservative one; at N = 1 the line also carries ONE call of the unmodified
+    reference ``LearnedIndex.search`` (oracle/_ref, staged by oracle/build_ref.py) on the same batch --
+    25 such calls would not fit the driver's window at 10M -- and the port on one thread."""
     if rank != 0:
         return
     C, nq, B = args.buckets, args.nq, (args.probe if args.probe > 0 else 4)
@@ -823,17 +1050,45 @@ def run_reference(args, wl_name, rank, world, local_rank):
     if use_cuda:
         torch.cuda.empty_cache()
     K, W = args.steps, max(1, args.warmup)
-    n_probe = min(nq, 200)
-    t_probe, _, _ = cb.run(n_probe, B)
-    S = pick_sample(t_probe, n_probe, nq, 150.0, K + W)
     for _ in range(W):
-        cb.run(S, B)
+        cb.run(B)
     t0 = time.perf_counter()
     for _ in range(K):
-        cb.run(S, B)
+        _, d_port, i_port, _ = cb.run(B)
     total = time.perf_counter() - t0
-    qps = S * K / total
-    sample = cb.describe(S, B, nq)
+    qps = nq * K / total
+    sample = cb.describe(B, nq)
+    log(f"reference arm (port): {K} steps x {nq} queries in {total:.1f}s = {qps:.1f} QPS on {cb.threads} threads")
+
+    extra = {}
+    if args.gpus == 1 and not args.no_reference_extras:
+        # one thread: what the README's "1 core" row is comparable with
+        try:
+            t1, _, _, _ = cb.run_single_thread(B)
+            extra["port_single_thread"] = {"value": nq / t1, "unit": "QPS", "cores": 1, "seconds": t1,
+                                           "sample": f"all {nq} queries, 1 call"}
+            log(f"reference arm (port, 1 thread): {t1:.1f}s = {nq / t1:.1f} QPS")
+        except Exception as e:  # noqa: BLE001
+            extra["port_single_thread"] = {"value": None, "note": f"failed: {e!r}"}
+        # the unmodified reference on the same batch, once
+        if cb.unmodified_available():
+            try:
+                t_ref, d_ref, i_ref, tm = cb.run_unmodified(B, limit_s=args.reference_limit)
+                same = bool(np.array_equal(i_ref, i_port))
+                extra["unmodified_reference"] = {
+                    "value": nq / t_ref, "unit": "QPS", "kind": "reference", "cores": cb.threads, "seconds": t_ref,
+                    "sample": f"all {nq} queries, 1 call of li.LearnedIndex.search (oracle/_ref, faiss.knn via "
+                              f"oracle/faiss_shim: torch sgemm + topk), frames view the pre-widened f32 matrix",
+                    "measured_time": {k_: float(v) for k_, v in tm.items()},
+                    "ids_equal_to_port": same,
+                    "max_abs_dist_diff_vs_port": float(np.nanmax(np.abs(np.where(np.isfinite(d_ref), d_ref - d_port, 0.0))))}
+                log(f"reference arm (unmodified li.LearnedIndex.search): {t_ref:.1f}s = {nq / t_ref:.1f} QPS; "
+                    f"ids equal to the port's: {same}")
+            except Exception as e:  # noqa: BLE001 -- RAM guard / time limit: say so, the port's number stands
+                extra["unmodified_reference"] = {"value": None, "kind": "reference", "note": f"not run: {e!r}"}
+        else:
+            extra["unmodified_reference"] = {"value": None, "kind": "reference",
+                                             "note": "oracle/_ref not staged (python -m oracle.build_ref)"}
     out = {
         "impl": "reference", "metric": "QPS at recall@10>=0.90", "value": qps, "unit": "QPS", "n_gpus": args.gpus,
         "steps": K, "warmup": W, "ms_per_step": total / K * 1e3, "higher_is_better": True, "scaling": "strong",
@@ -841,7 +1096,7 @@ def run_reference(args, wl_name, rank, world, local_rank):
         "config": {"workload": wl_name, "n": args.n, "nq": nq, "d": D, "n_buckets_in_index": C, "probed_buckets": B,
                    "k": K_NN},
         "cpu_baseline": {"value": qps, "unit": "QPS", "cores": cb.threads, "kind": "port", "sample": sample,
-                         "host_cpus": host_threads()},
+                         "host_cpus": host_threads(), "host_ram_gib": round(cb.ram_gb, 1), **extra},
         "e2e": {"value": qps, "unit": "QPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

@@ -52,7 +52,7 @@
 extern "C" {
 #endif
 
-#define LMI_B200_ABI_VERSION 3
+#define LMI_B200_ABI_VERSION 4
 
 #define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
 #define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
@@ -139,40 +139,76 @@ int lmi_navigate_tree(const float *node_prob, int nq, int n_nodes, const int32_t
 /* dst[dest_row[i], 0:d] = (fp16) src[i, :] for i < m, and dst[dest_row[i], d:dst_ld] = 0; src is
  * fp32 or fp16 [m,d], dst has a row pitch of dst_ld >= d elements (the scan kernel wants a
  * multiple of 64: zero columns leave every inner product unchanged).  dest_row == NULL is the
- * identity (cast + pad of a query matrix). */
+ * identity (cast + pad of a query matrix); a row with dest_row[i] < 0 is dropped (an object without
+ * a bucket).  inexact (optional, device int64, caller-zeroed): incremented by the number of fp32
+ * values the conversion to fp16 changed -- zero for data that is fp16 on disk and was widened, as
+ * SISAP's `emb` is after the reference's float32 casts (model.py:104, faiss.knn); non-zero means
+ * the scan runs on ROUNDED vectors (relative error 2^-11 per component), which the caller must
+ * surface (learnedmetricindex_b200 warns, or refuses with allow_fp16_rounding=False). */
 int lmi_scatter_rows(const void *src, int src_is_f16, const int64_t *dest_row, int64_t m, int d,
-                     void *dst_f16, int dst_ld, void *stream);
+                     void *dst_f16, int dst_ld, int64_t *inexact, void *stream);
 
-/* dst[i] = (fp16) src[i], count elements. */
-int lmi_cast_f16(const float *src, void *dst_f16, int64_t count, void *stream);
+/* dst[i] = (fp16) src[i], count elements; inexact as above. */
+int lmi_cast_f16(const float *src, void *dst_f16, int64_t count, int64_t *inexact, void *stream);
 
 /* ---- query-to-bucket inversion ------------------------------------------------ */
 
-/* Upper bound on the number of scan work items lmi_invert can emit. */
+/* Upper bound on the number of scan work items lmi_invert can emit (rmax = the most ranges any bucket
+ * is cut into, i.e. ceil(largest bucket / the SHORTER of range_len and tail_range_len)). */
 int64_t lmi_max_items(int nq, int B, int C, int rmax);
 /* int32 words of scratch lmi_invert needs (per-chunk histograms). */
 int64_t lmi_invert_workspace_ints(int nq, int B, int C);
 
+/* One allocation for everything a query batch needs between navigation and the final merge: byte offsets
+ * (256-byte aligned) of the arrays below inside a workspace of the returned size; offsets_host (HOST
+ * int64[LMI_WS_ARRAYS + 1], may be NULL) receives them, entry LMI_WS_ARRAYS the total.  Shapes depend only
+ * on (nq, B, C, rmax, d_pad), so a caller keeps one workspace per batch shape and a search allocates
+ * nothing.  d_pad = row pitch of the fp16 query copy (0: queries are fp16 with the layout's pitch already). */
+#define LMI_WS_COUNTS 0         /* int32[C]               lmi_invert counts        */
+#define LMI_WS_OFFSETS 1        /* int32[C+1]             lmi_invert offsets       */
+#define LMI_WS_BUCKET_LISTS 2   /* int32[C]               lmi_invert bucket_lists  */
+#define LMI_WS_PAIR_LIST 3      /* int32[nq*B]            lmi_invert pair_list     */
+#define LMI_WS_SLOT_OF_PAIR 4   /* int32[nq*B]            lmi_invert slot_of_pair  */
+#define LMI_WS_ITEMS 5          /* int32[max_items*8]     lmi_invert items         */
+#define LMI_WS_N_ITEMS 6        /* int32[2]               lmi_invert n_items       */
+#define LMI_WS_INVERT_SCRATCH 7 /* int32[lmi_invert_workspace_ints]                */
+#define LMI_WS_PART_SIM 8       /* f32[nq*B, 2*rmax, 10]  lmi_scan_topk part_sim   */
+#define LMI_WS_PART_ROW 9       /* int32[nq*B, 2*rmax, 10] lmi_scan_topk part_row  */
+#define LMI_WS_Q16 10           /* fp16[nq, d_pad]        cast / padded queries    */
+#define LMI_WS_ARRAYS 11
+int64_t lmi_workspace_layout(int nq, int B, int C, int rmax, int d_pad, int64_t *offsets_host);
+int64_t lmi_workspace_bytes(int nq, int B, int C, int rmax);
+
 /* Groups the nq*B (query, probe-rank) pairs by probed bucket -- ascending flat pair
  * index p = q*B + r inside a bucket, i.e. the order filter_path_idxs yields -- and
  * cuts the scan into work items.
- *   bucket_order int32[nq,B]   in   (entries outside [0,C) are ignored)
+ *   bucket_order int32[nq,B]   in   entries outside [0,C) are ignored, and so are probes of a bucket
+ *                                   that holds no rows in THIS layout (hi == lo in bucket_off: an empty
+ *                                   bucket, or one that lives on another GPU): slot -1, no item, the
+ *                                   merge pads them as the reference pads an empty bucket
  *   bucket_off   int64[C+1]    in   row range of bucket b in the bucket-major matrix
  *   range_len                  in   upper bound on the rows of a work item (multiple of 64); a
  *                                   bucket of s rows is cut into ceil(s / range_len) ranges of
  *                                   equal length, rounded up to a multiple of 64
- *   counts       int32[C]      out  m_b = pairs probing bucket b
+ *   tail_range_len, tail_permille   two-level cut: once (1000 - tail_permille)/1000 of the launch's work
+ *                                   (rows x query tiles, buckets in id order = the order the scan draws
+ *                                   items in) has been listed, buckets are cut with tail_range_len
+ *                                   (multiple of 64, < range_len) instead, so the persistent CTAs run dry
+ *                                   within a short item of each other; 0 / 0 = one level
+ *   counts       int32[C]      out  m_b = pairs probing bucket b (0 for a bucket without rows)
  *   offsets      int32[C+1]    out  exclusive scan of counts
  *   bucket_lists int32[C]      out  partial lists the scan writes per (query, bucket b) pair
  *                                   (= ranges of b x LMI_LISTS_PER_ITEM; 0 for an unprobed bucket)
  *   pair_list    int32[nq*B]   out  flat pair index per sorted slot
  *   slot_of_pair int32[nq*B]   out  inverse permutation (-1 for ignored pairs)
- *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, first list, bucket, 0, 0}
- *   n_items      int32[2]      out  [0] number of items; [1] scratch (the scan's scheduler counter)
+ *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, first list, bucket, query tile
+ *                                   index within (bucket, range), query tiles of the bucket}
+ *   n_items      int32[2]      out  [0] number of items; [1] = 0, the scan's item counter
  *   workspace    int32[lmi_invert_workspace_ints(nq,B,C)]  scratch
  */
 int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t *bucket_off,
-               int range_len, int32_t *counts, int32_t *offsets, int32_t *bucket_lists,
+               int range_len, int tail_range_len, int tail_permille,
+               int32_t *counts, int32_t *offsets, int32_t *bucket_lists,
                int32_t *pair_list, int32_t *slot_of_pair, int32_t *items, int32_t *n_items,
                int64_t max_items, int32_t *workspace, void *stream);
 

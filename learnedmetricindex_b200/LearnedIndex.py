@@ -18,7 +18,8 @@ from __future__ import annotations
 
 import os
 import time
-from collections import defaultdict
+import warnings
+from collections import OrderedDict, defaultdict
 from typing import Dict, List, Optional, Tuple
 
 import numpy as np
@@ -31,46 +32,94 @@ from .navigation import NavigationTree, flat_bucket_ids, unflatten_bucket_ids
 
 EMPTY_VALUE = -1  # search/li/PriorityQueue.py:4
 PER_BUCKET_K = 10  # `k` is not forwarded to _search_single_bucket (LearnedIndex.py:111-117, :334)
-MAX_RANGES = 32  # row ranges a bucket is cut into at most
+MAX_RANGES = 32  # row ranges a bucket is cut into at most (lmi_merge_topk: <= 256 lists, <= 32 in its fast path)
 LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
 DEFAULT_RANGE_ROWS = 24576  # upper bound on the rows of a scan work item (see plan_scan; sustained 10M sweep: 8192 +5 %, 16384 0, 24576 -1.9 %, 32768 -1.0 %)
-GRAPH_MAX_NQ = int(os.environ.get("LMI_GRAPH_MAX_NQ", 4096))  # `search` replays a CUDA graph up to this batch size
-GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index
+GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index (least recently used goes first)
+WS_CACHE = 8  # batch shapes whose workspace is kept
+WS_ARRAYS = 11  # LMI_WS_ARRAYS
+(WS_COUNTS, WS_OFFSETS, WS_BUCKET_LISTS, WS_PAIR_LIST, WS_SLOT_OF_PAIR, WS_ITEMS, WS_N_ITEMS, WS_INVERT_SCRATCH,
+ WS_PART_SIM, WS_PART_ROW, WS_Q16) = range(WS_ARRAYS)
 
 
 def _stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
-def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_bucket: int,
-              n_sms: int = 148, items_per_sm: int = 8) -> Tuple[int, int]:
-    """Rows per scan work item (multiple of 64) and the resulting ranges per bucket.
+def _round_up(v: int, m: int) -> int:
+    return -(-int(v) // m) * m
 
-    Work items are (bucket, row range, tile of 128 probing queries).  Aim at
-    ``items_per_sm`` items per SM so the static round-robin over persistent CTAs balances,
-    keep ranges long so the per-item top-10 warm-up and query gather amortise, and never
-    exceed ``MAX_RANGES`` lists per (query, probe)."""
-    pairs = max(1, nq * n_probe)
-    touched = min(n_buckets_in_index, pairs)
-    tiles = max(touched, -(-pairs // 128))  # sum_b ceil(m_b / 128), roughly
-    mean_bucket = max(1, n_rows // max(1, n_buckets_in_index))
-    total_rows = tiles * mean_bucket
-    want = max(1, n_sms * items_per_sm)
-    length = -(-total_rows // want)
-    # short ranges keep the dynamic schedule balanced and the query tiles of a range within an L2
-    # window of each other; long enough that the per-item query gather and top-10 warm-up amortise
-    length = min(length, int(os.environ.get("LMI_RANGE_ROWS", DEFAULT_RANGE_ROWS)))
-    length = max(length, 1024, -(-max_bucket // MAX_RANGES))
-    length = min(length, max(max_bucket, SCAN_ROWS_PER_TILE))
-    length = -(-length // SCAN_ROWS_PER_TILE) * SCAN_ROWS_PER_TILE
-    rmax = max(1, -(-max_bucket // length))
+
+def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_bucket: int,
+              n_sms: int = 148, n_nonempty: Optional[int] = None) -> Dict[str, int]:
+    """How ``lmi_invert`` cuts the probed buckets into scan work items.
+
+    Work items are (bucket, row range, tile of 128 probing queries), drawn in list order by the scan's
+    persistent CTAs.  Two lengths (rows per item): ``range_len`` while there is plenty of work -- long, so
+    the per-item query gather and top-10 warm-up amortise -- and a shorter ``tail_range_len`` for the last
+    ``tail_permille`` of the launch's work, so the CTAs run dry within a short item of each other (with one
+    length the ragged end of the launch is about half a long item per SM).  ``n_nonempty``: buckets that hold
+    rows in THIS layout (a rank of a sharded index owns only some); the estimate of the per-SM work uses it.
+    Returns ``dict(range_len, tail_range_len, tail_permille, rmax)``; ``rmax`` = most ranges of any bucket."""
+    C = max(1, n_buckets_in_index)
+    local = C if n_nonempty is None else max(1, min(C, n_nonempty))
+    pairs = max(1.0, nq * n_probe * local / C)  # probes that land in a bucket held here
+    tiles = max(min(local, pairs), pairs / 128.0)  # sum_b ceil(m_b / 128), roughly
+    mean_bucket = max(1.0, n_rows / local)
+    rows_per_sm = tiles * mean_bucket / max(1, n_sms)  # rows (x 128 queries) one CTA scans in the launch
+    floor_rows = max(1024, -(-max_bucket // MAX_RANGES))
+    env = os.environ.get
+    main = int(env("LMI_RANGE_ROWS", 0)) or int(min(DEFAULT_RANGE_ROWS, max(rows_per_sm / 6.0, 2048.0)))
+    main = max(main, floor_rows)
+    main = _round_up(min(main, max(max_bucket, SCAN_ROWS_PER_TILE)), SCAN_ROWS_PER_TILE)
+    tail = int(env("LMI_TAIL_ROWS", 0)) or main // 3
+    # keep every bucket within 16 ranges (= 32 partial lists per probe: the merge's one-list-per-lane path)
+    tail = _round_up(max(tail, floor_rows, -(-max_bucket // 16)), SCAN_ROWS_PER_TILE)
+    permille = env("LMI_TAIL_PERMILLE")
+    if permille is not None:
+        permille = int(permille)
+    else:
+        # the short items should cover about the last 1.25 long items of every SM
+        permille = int(min(400.0, max(50.0, 1250.0 * main / max(rows_per_sm, 1.0))))
+    if tail >= main:
+        tail, permille = 0, 0
+    rmax = max(1, -(-max_bucket // (tail or main)))
     assert rmax <= MAX_RANGES
-    return length, rmax
+    return dict(range_len=main, tail_range_len=tail, tail_permille=permille, rmax=rmax)
+
+
+class _BatchWorkspace:
+    """Every transient array of one batch shape, in ONE allocation carved by ``lmi_workspace_layout``
+    (SURVEY.md section 8b): a search allocates nothing but its two small result tensors."""
+
+    def __init__(self, lib, layout: DeviceBucketLayout, nq: int, B: int, n_sms: int, q_needs_copy: bool):
+        import ctypes
+
+        self.nq, self.B = nq, B
+        C = layout.n_buckets
+        self.plan = plan_scan(nq, B, C, layout.n, layout.max_bucket, n_sms, layout.n_nonempty)
+        self.rmax = self.plan["rmax"]
+        self.lmax = self.rmax * LISTS_PER_ITEM
+        self.max_items = int(lib.lmi_max_items(nq, B, C, self.rmax))
+        offs = (ctypes.c_int64 * (WS_ARRAYS + 1))()
+        total = int(lib.lmi_workspace_layout(nq, B, C, self.rmax, layout.d if q_needs_copy else 0, offs))
+        assert total > 0
+        self.buf = torch.empty(total, dtype=torch.uint8, device=layout.device)
+        base = self.buf.data_ptr()
+        self.ptr = [base + int(offs[i]) for i in range(WS_ARRAYS)]
+        self.counts = self.buf[int(offs[WS_COUNTS]): int(offs[WS_COUNTS]) + 4 * C].view(torch.int32)
+        self.n_items = self.buf[int(offs[WS_N_ITEMS]): int(offs[WS_N_ITEMS]) + 8].view(torch.int32)
+        self.q16 = None
+        if q_needs_copy:
+            o = int(offs[WS_Q16])
+            self.q16 = self.buf[o: o + 2 * nq * layout.d].view(torch.float16).view(nq, layout.d)
+        self.inexact = torch.zeros(1, dtype=torch.int64, device=layout.device)  # queries changed by the fp16 cast
 
 
 class LearnedIndex:
-    def __init__(self, root_model, internal_models=None, bucket_paths=None, scan_impl: int = 0):
+    def __init__(self, root_model, internal_models=None, bucket_paths=None, scan_impl: int = 0,
+                 allow_fp16_rounding: Optional[bool] = None):
         self.root_model = NeuralNetwork.from_reference(root_model)
         """The root model of the index."""
         self.internal_models = {tuple(p): NeuralNetwork.from_reference(m) for p, m in (internal_models or {}).items()}
@@ -78,6 +127,10 @@ class LearnedIndex:
         self.bucket_paths = [tuple(p) for p in (bucket_paths or [])]
         """List of paths to the buckets."""
         self.scan_impl = scan_impl  # 0: tcgen05/TMA kernel; 1: CUDA-core verification kernel (tests)
+        # The scan computes f32 arithmetic on fp16 values -- exactly the reference's arithmetic when the data is
+        # fp16 on disk (SISAP `emb`).  f32 data that fp16 cannot represent is ROUNDED (2^-11 relative per
+        # component): None = warn once, True = accept silently, False = refuse (ValueError).
+        self.allow_fp16_rounding = allow_fp16_rounding
         self.use_graphs = os.environ.get("LMI_CUDA_GRAPH", "1") != "0"
         self.device = self.root_model.device
         self._layout: Optional[DeviceBucketLayout] = None
@@ -85,9 +138,13 @@ class LearnedIndex:
         self._layout_refs = None
         self.last_bucket_order: Optional[torch.Tensor] = None
         self.last_probs: Optional[torch.Tensor] = None
+        self.last_plan: Optional[dict] = None
         self._tree: Optional[NavigationTree] = None
-        self._graphs: Dict[tuple, dict] = {}
+        self._graphs: "OrderedDict[tuple, dict]" = OrderedDict()
+        self._workspaces: "OrderedDict[tuple, _BatchWorkspace]" = OrderedDict()
+        self._warned_rounding = False
         self._n_sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self.scan_flags = int(os.environ.get("LMI_SCAN_FLAGS", "0"))  # lmi_scan_topk tuning flags (results identical)
 
     @classmethod
     def from_reference(cls, li, **kw) -> "LearnedIndex":
@@ -100,19 +157,39 @@ class LearnedIndex:
         models and bucket paths; the device layout, like ``data_prediction`` in the reference
         (search.py:228), is not part of the pickle and is rebuilt by the first ``search``."""
         return {"root_model": self.root_model, "internal_models": self.internal_models,
-                "bucket_paths": self.bucket_paths, "scan_impl": self.scan_impl}
+                "bucket_paths": self.bucket_paths, "scan_impl": self.scan_impl,
+                "allow_fp16_rounding": self.allow_fp16_rounding}
 
     def __setstate__(self, state):
         self.__init__(state["root_model"], state["internal_models"], state["bucket_paths"],
-                      scan_impl=state.get("scan_impl", 0))
+                      scan_impl=state.get("scan_impl", 0), allow_fp16_rounding=state.get("allow_fp16_rounding"))
 
     # ------------------------------------------------------------------ layout ------
+    def _forget_layout_state(self):
+        self._graphs.clear()  # captured graphs hold pointers into the previous layout
+        self._workspaces.clear()
+
+    def _check_rounding(self, inexact: int, what: str):
+        """fp16 storage changed ``inexact`` values of ``what``: refuse, warn once, or accept."""
+        if inexact <= 0 or self.allow_fp16_rounding is True:
+            return
+        msg = (f"{inexact} values of {what} are not representable in fp16 and were rounded (relative error <= 2^-11 "
+               f"per component; distances of unit vectors move by up to ~5e-4, typically ~1e-5): the scan computes "
+               f"f32 arithmetic on fp16 values, which equals the reference's arithmetic only for data that is fp16 "
+               f"on disk (SISAP `emb`).  Pass allow_fp16_rounding=True to accept, False to refuse.")
+        if self.allow_fp16_rounding is False:
+            raise ValueError(msg)
+        if not self._warned_rounding:
+            warnings.warn(msg, UserWarning, stacklevel=3)
+            self._warned_rounding = True
+
     def attach_layout(self, layout: DeviceBucketLayout) -> None:
         """Use a device layout built elsewhere (e.g. data generated on the GPU)."""
+        self._check_rounding(layout.inexact_values, "data_search")
         self._layout = layout
         self._layout_key = "attached"
         self._layout_refs = None
-        self._graphs.clear()  # captured graphs hold pointers into the previous layout
+        self._forget_layout_state()
 
     def prepare(self, data_search, data_prediction, n_categories, data_navigation=None) -> DeviceBucketLayout:
         """Build (once) the bucket-major device layout for ``data_search`` / ``data_prediction``."""
@@ -137,11 +214,12 @@ class LearnedIndex:
             ids = np.asarray(data_navigation.index)
             if hasattr(data_search, "index") and not data_search.index.equals(data_navigation.index):
                 data_search = data_search.loc[data_navigation.index]  # label lookup, as :357 does
-        self._layout = DeviceBucketLayout.from_host(data_search, labels, n_layout_buckets, ids=ids,
-                                                    device=self.device)
+        layout = DeviceBucketLayout.from_host(data_search, labels, n_layout_buckets, ids=ids, device=self.device)
+        self._check_rounding(layout.inexact_values, "data_search")
+        self._layout = layout
         self._layout_key = key
         self._layout_refs = (data_search, data_prediction)  # keep ids from being recycled
-        self._graphs.clear()
+        self._forget_layout_state()
         return self._layout
 
     # ------------------------------------------------------------------ navigation --
@@ -173,11 +251,25 @@ class LearnedIndex:
         return unflatten_bucket_ids(order, n_categories), e0.elapsed_time(e1) / 1e3
 
     # ------------------------------------------------------------------ search ------
+    def _workspace(self, nq: int, B: int, q_needs_copy: bool) -> _BatchWorkspace:
+        key = (nq, B, bool(q_needs_copy), id(self._layout))
+        ws = self._workspaces.get(key)
+        if ws is None:
+            if len(self._workspaces) >= WS_CACHE:
+                self._workspaces.popitem(last=False)
+            ws = _BatchWorkspace(_native.lib(), self._layout, nq, B, self._n_sms, q_needs_copy)
+            self._workspaces[key] = ws
+        else:
+            self._workspaces.move_to_end(key)
+        return ws
+
     def search_device(self, qn: torch.Tensor, qs: torch.Tensor, n_categories: List[int], n_buckets: int, k: int,
                       events=None, out=None, bucket_order: Optional[torch.Tensor] = None):
         """Everything between the H2D and D2H copies.  ``qn`` / ``qs``: device matrices
         (fp16 or f32).  Returns device tensors (dists f64[nq,k'], nns int32-bits[nq,k']);
-        ``out=(dists, nns)`` supplies them (e.g. views into an all-gather send buffer)."""
+        ``out=(dists, nns)`` supplies them (e.g. views into an all-gather send buffer).
+        All transient arrays live in a per-shape workspace that is reused by the next search of the
+        same shape on this index: one stream at a time per index (the reference is single-threaded too)."""
         L = _native.lib()
         layout = self._layout
         assert layout is not None, "call prepare()/attach_layout() first"
@@ -214,100 +306,115 @@ class LearnedIndex:
                 mark(i)
             return dists, nns
 
+        needs_copy = layout.d != layout.d_data or qs.dtype != torch.float16
+        ws = self._workspace(nq, B, needs_copy)
+        st = _stream_ptr()
         if layout.d != layout.d_data:  # zero-pad K to the scan kernel's multiple of 64
-            q16 = torch.empty((nq, layout.d), dtype=torch.float16, device=dev)
+            q16 = ws.q16
             _native.check(L.lmi_scatter_rows(qs.data_ptr(), int(qs.dtype == torch.float16), None, nq, layout.d_data,
-                                             q16.data_ptr(), layout.d, _stream_ptr()), "lmi_scatter_rows")
+                                             q16.data_ptr(), layout.d, ws.inexact.data_ptr(), st), "lmi_scatter_rows")
         elif qs.dtype == torch.float16:
             q16 = qs
         else:
-            q16 = torch.empty(qs.shape, dtype=torch.float16, device=dev)
-            _native.check(L.lmi_cast_f16(qs.data_ptr(), q16.data_ptr(), qs.numel(), _stream_ptr()), "lmi_cast_f16")
+            q16 = ws.q16
+            _native.check(L.lmi_cast_f16(qs.data_ptr(), q16.data_ptr(), qs.numel(), ws.inexact.data_ptr(), st),
+                          "lmi_cast_f16")
+        self._last_ws = ws
 
-        range_len, rmax = plan_scan(nq, B, C, layout.n, layout.max_bucket, self._n_sms)
-        P = nq * B
-        max_items = int(L.lmi_max_items(nq, B, C, rmax))
-        lmax = rmax * LISTS_PER_ITEM
-        counts = torch.empty(C, dtype=torch.int32, device=dev)
-        bucket_lists = torch.empty(C, dtype=torch.int32, device=dev)
-        offsets = torch.empty(C + 1, dtype=torch.int32, device=dev)
-        pair_list = torch.empty(P, dtype=torch.int32, device=dev)
-        slot_of_pair = torch.empty(P, dtype=torch.int32, device=dev)
-        items = torch.empty(max_items * 8, dtype=torch.int32, device=dev)
-        n_items = torch.zeros(2, dtype=torch.int32, device=dev)
-        work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
-        _native.check(L.lmi_invert(order.data_ptr(), nq, B, C, layout.bucket_off.data_ptr(), range_len,
-                                   counts.data_ptr(), offsets.data_ptr(), bucket_lists.data_ptr(), pair_list.data_ptr(),
-                                   slot_of_pair.data_ptr(), items.data_ptr(), n_items.data_ptr(), max_items,
-                                   work.data_ptr(), _stream_ptr()), "lmi_invert")
+        plan, P = ws.plan, ws.ptr
+        _native.check(L.lmi_invert(order.data_ptr(), nq, B, C, layout.bucket_off.data_ptr(), plan["range_len"],
+                                   plan["tail_range_len"], plan["tail_permille"], P[WS_COUNTS], P[WS_OFFSETS],
+                                   P[WS_BUCKET_LISTS], P[WS_PAIR_LIST], P[WS_SLOT_OF_PAIR], P[WS_ITEMS], P[WS_N_ITEMS],
+                                   ws.max_items, P[WS_INVERT_SCRATCH], st), "lmi_invert")
         mark(2)
-
-        part_sim = torch.empty(P * lmax * PER_BUCKET_K, dtype=torch.float32, device=dev)
-        part_row = torch.empty(P * lmax * PER_BUCKET_K, dtype=torch.int32, device=dev)
         if layout.n > 0:
             _native.check(L.lmi_scan_topk(layout.vectors.data_ptr(), layout.n, layout.d, q16.data_ptr(), nq, B,
-                                          pair_list.data_ptr(), items.data_ptr(), n_items.data_ptr(), max_items,
-                                          lmax, part_sim.data_ptr(), part_row.data_ptr(), self.scan_impl,
-                                          _stream_ptr()), "lmi_scan_topk")
+                                          P[WS_PAIR_LIST], P[WS_ITEMS], P[WS_N_ITEMS], ws.max_items, ws.lmax,
+                                          P[WS_PART_SIM], P[WS_PART_ROW], self.scan_impl | (self.scan_flags << 8), st),
+                          "lmi_scan_topk")
         mark(3)
-        _native.check(L.lmi_merge_topk(part_sim.data_ptr(), part_row.data_ptr(), slot_of_pair.data_ptr(),
-                                       order.data_ptr(), layout.bucket_off.data_ptr(), layout.ids.data_ptr(),
-                                       bucket_lists.data_ptr(), nq, B, C, lmax, k_out, dists.data_ptr(),
-                                       nns.data_ptr(), _stream_ptr()),
-                      "lmi_merge_topk")
+        _native.check(L.lmi_merge_topk(P[WS_PART_SIM], P[WS_PART_ROW], P[WS_SLOT_OF_PAIR], order.data_ptr(),
+                                       layout.bucket_off.data_ptr(), layout.ids.data_ptr(), P[WS_BUCKET_LISTS], nq, B,
+                                       C, ws.lmax, k_out, dists.data_ptr(), nns.data_ptr(), st), "lmi_merge_topk")
         mark(4)
-        self.last_plan = dict(range_len=range_len, rmax=rmax, max_items=max_items, n_items=n_items,
-                              counts=counts)
+        self.last_plan = dict(plan, max_items=ws.max_items, n_items=ws.n_items, counts=ws.counts)
         return dists, nns
+
+    @property
+    def launches_per_search(self) -> int:
+        """Kernels of this library one 1-level search launches (navigation + inversion + scan + merge)."""
+        return self.root_model.launches_per_topn + 3 + 1 + 1
+
+    def _surface_query_rounding(self):
+        """After a host-visible sync: did the fp16 copy of the last f32 query batch change any value?"""
+        ws = getattr(self, "_last_ws", None)
+        if ws is None or ws.q16 is None or self.allow_fp16_rounding is True or self._warned_rounding:
+            return
+        n = int(ws.inexact.item())
+        if n:
+            ws.inexact.zero_()
+            self._check_rounding(n, "queries_search")
 
     # ------------------------------------------------------------------ CUDA graph --
     def search_graphed(self, qn, qs, n_categories: List[int], n_buckets: int, k: int):
-        """``search_device`` as ONE CUDA-graph replay: the ~15 launches of a search (split, Linear
-        layers, softmax/top-n or tree navigation, inversion, scan, merge) are captured once per
-        (batch shape, budget) with static input/output buffers, so a small batch costs one graph
-        launch instead of ~15 host-side launches.  ``qn`` / ``qs`` may be host (numpy / pinned
-        torch) or device matrices; they are copied into the static inputs.  Returns
-        ``(dists, nns, stage_ms)`` -- the static output tensors, valid until the next replay of the
-        same shape, and the per-stage milliseconds of the eager run made at capture time."""
+        """``search_device`` as ONE CUDA-graph replay, for any batch size: the launches of a search
+        (navigation, inversion, scan, merge) are captured once per (batch shape, budget) with static
+        input/output buffers -- the only shape-dependent data, the work-item list and its length, is
+        produced on the device -- so a search costs one graph launch on the host.  ``qn`` / ``qs`` may be
+        host (numpy / pinned torch) or device matrices; they are copied into the static inputs.
+        Stage timings come from event-record nodes inside the graph, i.e. they are THIS replay's.
+        Returns ``(dists, nns, events)`` -- the static output tensors, valid until the next replay of
+        the same shape, and the five stage events (read them after synchronising)."""
         shared = qs is qn
+
         def as_tensor(x):
             if isinstance(x, torch.Tensor):
-                return x
-            a = np.asarray(x)
-            if a.dtype not in (np.float16, np.float32):
-                a = a.astype(np.float32)  # model.py:104
-            return torch.from_numpy(np.ascontiguousarray(a))
+                t = x
+            else:
+                a = np.asarray(x)
+                if a.dtype not in (np.float16, np.float32):
+                    a = a.astype(np.float32)  # model.py:104
+                t = torch.from_numpy(np.ascontiguousarray(a))
+            return t if t.dtype in (torch.float16, torch.float32) else t.float()  # as to_device_matrix does
+
         tn = as_tensor(qn)
         ts = tn if shared else as_tensor(qs)
+        # a contiguous DEVICE matrix is read in place (the graph is keyed on its address); anything else is
+        # copied into a static device buffer before every replay
+        in_place = lambda t: t.is_cuda and t.is_contiguous()
         key = (tuple(tn.shape), tn.dtype, tuple(ts.shape), ts.dtype, shared, tuple(n_categories), int(n_buckets),
-               int(k), id(self._layout), self.scan_impl)
+               int(k), id(self._layout), self.scan_impl, tn.data_ptr() if in_place(tn) else 0,
+               ts.data_ptr() if in_place(ts) else 0)
         entry = self._graphs.get(key)
         if entry is None:
             if len(self._graphs) >= GRAPH_CACHE:
-                self._graphs.pop(next(iter(self._graphs)))
-            sn = torch.empty(tn.shape, dtype=tn.dtype, device=self.device)
-            ss = sn if shared else torch.empty(ts.shape, dtype=ts.dtype, device=self.device)
-            sn.copy_(tn, non_blocking=True)
-            if not shared:
+                self._graphs.popitem(last=False)  # least recently used
+            sn = tn if in_place(tn) else torch.empty(tn.shape, dtype=tn.dtype, device=self.device)
+            ss = sn if shared else (ts if in_place(ts) else torch.empty(ts.shape, dtype=ts.dtype, device=self.device))
+            if sn is not tn:
+                sn.copy_(tn, non_blocking=True)
+            if not shared and ss is not ts:
                 ss.copy_(ts, non_blocking=True)
-            # eager run first: fills every lazy cache (weight splits, tensor-map driver entry point, the
-            # navigation tree) outside the capture and yields the per-stage timings
-            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
-            self.search_device(sn, ss, n_categories, n_buckets, k, events=ev)
+            # eager run first: fills every lazy cache (weight splits, workspaces, the tensor-map driver entry
+            # point, the navigation tree) outside the capture
+            d, i = self.search_device(sn, ss, n_categories, n_buckets, k)
             torch.cuda.current_stream().synchronize()
-            stage_ms = [ev[j].elapsed_time(ev[j + 1]) for j in range(4)]
+            ev = [torch.cuda.Event(enable_timing=True, external=True) for _ in range(5)]
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                d, i = self.search_device(sn, ss, n_categories, n_buckets, k)
-            entry = dict(graph=graph, qn=sn, qs=ss, dists=d, nns=i, stage_ms=stage_ms, order=self.last_bucket_order)
+                d, i = self.search_device(sn, ss, n_categories, n_buckets, k, events=ev, out=(d, i))
+            entry = dict(graph=graph, qn=sn, qs=ss, dists=d, nns=i, events=ev, order=self.last_bucket_order,
+                         plan=self.last_plan)
             self._graphs[key] = entry
         else:
-            entry["qn"].copy_(tn, non_blocking=True)
-            if not shared:
+            self._graphs.move_to_end(key)
+            if entry["qn"] is not tn:
+                entry["qn"].copy_(tn, non_blocking=True)
+            if not shared and entry["qs"] is not ts:
                 entry["qs"].copy_(ts, non_blocking=True)
         entry["graph"].replay()
-        self.last_bucket_order = entry["order"]
-        return entry["dists"], entry["nns"], entry["stage_ms"]
+        self.last_bucket_order, self.last_plan = entry["order"], entry["plan"]
+        return entry["dists"], entry["nns"], entry["events"]
 
     def search(
         self,
@@ -334,23 +441,20 @@ class LearnedIndex:
             self.prepare(data_search, data_prediction, n_categories, data_navigation)
         assert self._layout is not None, "no index data: pass data_search/data_prediction or attach_layout()"
 
-        if 0 < len(queries_search) <= GRAPH_MAX_NQ and self.use_graphs:
-            # latency-bound batch sizes: one graph replay; the stage split reported is the one measured
-            # when this shape was captured, "search" is this call's wall time
-            dists_d, nns_d, st = self.search_graphed(
+        if len(queries_search) > 0 and self.use_graphs:
+            # one graph replay per search; the stage split is read from event nodes inside the graph
+            dists_d, nns_d, ev = self.search_graphed(
                 queries_navigation, queries_navigation if queries_search is queries_navigation else queries_search,
                 n_categories, n_buckets, k)
-            dists = dists_d.cpu().numpy()
-            nns = nns_d.cpu().numpy().view(np.uint32)
-            stage = [t / 1e3 for t in st]
         else:
             qn = to_device_matrix(queries_navigation, self.device)
             qs = qn if queries_search is queries_navigation else to_device_matrix(queries_search, self.device)
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
             dists_d, nns_d = self.search_device(qn, qs, n_categories, n_buckets, k, events=ev)
-            dists = dists_d.cpu().numpy()
-            nns = nns_d.cpu().numpy().view(np.uint32)
-            stage = [ev[j].elapsed_time(ev[j + 1]) / 1e3 for j in range(4)]
+        dists = dists_d.cpu().numpy()
+        nns = nns_d.cpu().numpy().view(np.uint32)
+        stage = [ev[j].elapsed_time(ev[j + 1]) / 1e3 for j in range(4)]
+        self._surface_query_rounding()
 
         measured_time["inference"] = stage[0]
         measured_time["search_within_buckets"] = stage[1] + stage[2] + stage[3]

@@ -69,12 +69,14 @@ _SIGNATURES = {
     "lmi_softmax_probs": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p]),
     "lmi_navigate_tree": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p,
                                   c_void_p]),
-    "lmi_scatter_rows": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_void_p, c_int, c_void_p]),
-    "lmi_cast_f16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "lmi_scatter_rows": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "lmi_cast_f16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "lmi_max_items": (c_int64, [c_int, c_int, c_int, c_int]),
     "lmi_invert_workspace_ints": (c_int64, [c_int, c_int, c_int]),
-    "lmi_invert": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
-                           c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "lmi_workspace_layout": (c_int64, [c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "lmi_workspace_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
+    "lmi_invert": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                           c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "lmi_scan_topk": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
                               c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "lmi_merge_topk": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

@@ -108,6 +108,9 @@ def _torch_model(in_dim: int, out_dim: int, model_type: str, device) -> torch.nn
     return torch.nn.Sequential(*mods).to(device)
 
 
+kmeans_gpu.accepts_device_tensor = True  # every other callable gets the reference's numpy contract
+
+
 class LearnedIndexBuilder:
     """search/li/LearnedIndexBuilder.py:21-280.  ``data``: DataFrame / ndarray / device tensor
     [n, d]; row i carries the label i+1, as the reference assumes (:247, :270)."""
@@ -142,8 +145,14 @@ class LearnedIndexBuilder:
             if n < k:  # :291-294
                 k = max(2, n // 5)
             algo = clustering_algorithm if callable(clustering_algorithm) else kmeans_gpu
-            _, labels = algo(x, k, None)
-            labels = torch.as_tensor(labels, device=self.device).to(torch.int64)
+            if getattr(algo, "accepts_device_tensor", False):
+                _, labels = algo(x, k, None)
+            else:
+                # the reference's contract (clustering/faiss_kmeans.py:8-24, scikit_kmeans.py:8-29):
+                # (np.ndarray f32 [n, d], n_clusters, parameters) -> (object, labels)
+                _, labels = algo(x.float().cpu().numpy(), k, None)
+            labels = torch.as_tensor(np.asarray(labels).reshape(-1) if not isinstance(labels, torch.Tensor) else labels,
+                                     device=self.device).to(torch.int64)
         torch.cuda.synchronize(self.device)
         cluster_t = time.time() - t0
         # labels are used as class ids as they are (:166-168); the class count is the number of

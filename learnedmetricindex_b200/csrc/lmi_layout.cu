@@ -10,34 +10,59 @@
 
 namespace lmi {
 
-// one warp per source row; 8-byte (4 x fp16) stores
+// one warp per source row.  Rows with dest_row[i] < 0 are dropped (objects without a bucket).
+// `inexact` (optional) counts the values the fp32 -> fp16 conversion changed: the scan computes
+// f32 arithmetic on fp16-representable values (what SISAP's fp16 `emb` gives the reference after
+// its float32 casts), so a non-zero count means the distances are those of ROUNDED vectors.
 template <typename T>
 __global__ void scatter_rows_kernel(const T* __restrict__ src, const int64_t* __restrict__ dest_row, int64_t m, int d,
-                                    __half* __restrict__ dst, int ld) {
+                                    __half* __restrict__ dst, int ld, unsigned long long* __restrict__ inexact) {
     const int warps = blockDim.x >> 5;
     const int lane = threadIdx.x & 31;
+    int bad = 0;
     for (int64_t i = (int64_t)blockIdx.x * warps + (threadIdx.x >> 5); i < m; i += (int64_t)gridDim.x * warps) {
         const int64_t to = dest_row ? dest_row[i] : i;
+        if (to < 0) continue;
         const T* s = src + (size_t)i * d;
         __half* o = dst + (size_t)to * ld;
         for (int c = lane; c < d; c += 32) {
-            if constexpr (sizeof(T) == 2) o[c] = s[c];
-            else o[c] = __float2half_rn(static_cast<float>(s[c]));
+            if constexpr (sizeof(T) == 2) {
+                o[c] = s[c];
+            } else {
+                const float v = static_cast<float>(s[c]);
+                const __half h = __float2half_rn(v);
+                o[c] = h;
+                bad += (__half2float(h) != v && v == v) ? 1 : 0;
+            }
         }
         for (int c = d + lane; c < ld; c += 32) o[c] = __float2half_rn(0.f);  // zero padding: inner products unchanged
     }
+    if (inexact) {
+        bad = __reduce_add_sync(0xffffffffu, bad);
+        if (lane == 0 && bad) atomicAdd(inexact, (unsigned long long)bad);
+    }
 }
 
-__global__ void cast_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, int64_t count) {
+__global__ void cast_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, int64_t count,
+                                unsigned long long* __restrict__ inexact) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
-        dst[i] = __float2half_rn(src[i]);
+    int bad = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const float v = src[i];
+        const __half h = __float2half_rn(v);
+        dst[i] = h;
+        bad += (__half2float(h) != v && v == v) ? 1 : 0;
+    }
+    if (inexact) {
+        bad = __reduce_add_sync(0xffffffffu, bad);
+        if ((threadIdx.x & 31) == 0 && bad) atomicAdd(inexact, (unsigned long long)bad);
+    }
 }
 
 }  // namespace lmi
 
 extern "C" int lmi_scatter_rows(const void* src, int src_is_f16, const int64_t* dest_row, int64_t m, int d,
-                                void* dst_f16, int dst_ld, void* stream) {
+                                void* dst_f16, int dst_ld, int64_t* inexact, void* stream) {
     if (!src || !dst_f16 || m < 0 || d <= 0 || dst_ld < d) return LMI_E_BADARG;
     if (m == 0) return 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -47,21 +72,24 @@ extern "C" int lmi_scatter_rows(const void* src, int src_is_f16, const int64_t* 
     if (src_is_f16)
         lmi::scatter_rows_kernel<__half><<<(unsigned)grid, warps * 32, 0, st>>>(static_cast<const __half*>(src),
                                                                                dest_row, m, d,
-                                                                               static_cast<__half*>(dst_f16), dst_ld);
+                                                                               static_cast<__half*>(dst_f16), dst_ld,
+                                                                               nullptr);
     else
         lmi::scatter_rows_kernel<float><<<(unsigned)grid, warps * 32, 0, st>>>(static_cast<const float*>(src),
                                                                               dest_row, m, d,
-                                                                              static_cast<__half*>(dst_f16), dst_ld);
+                                                                              static_cast<__half*>(dst_f16), dst_ld,
+                                                                              reinterpret_cast<unsigned long long*>(inexact));
     return static_cast<int>(cudaGetLastError());
 }
 
-extern "C" int lmi_cast_f16(const float* src, void* dst_f16, int64_t count, void* stream) {
+extern "C" int lmi_cast_f16(const float* src, void* dst_f16, int64_t count, int64_t* inexact, void* stream) {
     if (!src || !dst_f16 || count < 0) return LMI_E_BADARG;
     if (count == 0) return 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int64_t grid = (count + 255) / 256;
     if (grid > 148 * 32) grid = 148 * 32;
-    lmi::cast_f16_kernel<<<(unsigned)grid, 256, 0, st>>>(src, static_cast<__half*>(dst_f16), count);
+    lmi::cast_f16_kernel<<<(unsigned)grid, 256, 0, st>>>(src, static_cast<__half*>(dst_f16), count,
+                                                         reinterpret_cast<unsigned long long*>(inexact));
     return static_cast<int>(cudaGetLastError());
 }
 

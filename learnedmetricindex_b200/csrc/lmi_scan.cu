@@ -51,8 +51,18 @@ constexpr int SCAN_SCHED_SLOTS = 4;   // item indices the producer may run ahead
 constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ +
                                    2 * SCAN_M * sizeof(float) /*gates*/;
 
-// profiling aid (LMI_SCAN_ABLATE & 8): per CTA, cycles the MMA warp spent waiting on each barrier
+// Scan tuning flags (lmi_scan_topk's `impl` >> 8): results are identical for every value.
+constexpr int SCAN_FLAG_L2_SIBLINGS = 1;  // L2 eviction hints by sibling order (see the producer)
+
+#ifdef LMI_PROFILE
+// profiling build only (tools/): `dbg` ablations give WRONG results and are compiled out of the product
+// (dbg & 1: no TMA loads; & 2: no candidate processing; & 4: half the operand traffic; & 8: MMA-warp
+// wait cycles per CTA into g_scan_prof)
 __device__ long long g_scan_prof[148 * 8];
+#define LMI_DBG(x) (x)
+#else
+#define LMI_DBG(x) 0
+#endif
 
 struct ScanBarriers {
     uint64_t full[SCAN_STAGES];
@@ -112,7 +122,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 1)
 scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __restrict__ Q,
                     const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
                     const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int lmax,
-                    float* __restrict__ part_sim, int32_t* __restrict__ part_row, int dbg) {
+                    float* __restrict__ part_sim, int32_t* __restrict__ part_row, int flags, int dbg) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     ScanBarriers* bars = reinterpret_cast<ScanBarriers*>(stages + (size_t)SCAN_STAGES * SCAN_STAGE_BYTES);
@@ -171,7 +181,13 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         // ===================== TMA producer =====================
         // The whole warp walks the loop (warp-uniform control flow); one elected lane issues, so
         // ptxas emits the TMA / mbarrier instructions straight, without a per-thread waterfall loop.
-        const uint64_t policy = ptx::policy_evict_normal();
+        // The query tiles of one (bucket, row range) are adjacent items, drawn back to back by different CTAs:
+        // the first reader pulls the rows from HBM, its siblings should find them in L2.  With
+        // SCAN_FLAG_L2_SIBLINGS every tile but the last of a range loads with evict_last (keep the rows for
+        // the siblings still to come) and the last one with evict_first (nobody reads them again this launch).
+        const uint64_t pol_normal = ptx::policy_evict_normal();
+        const uint64_t pol_keep = ptx::policy_evict_last();
+        const uint64_t pol_drop = ptx::policy_evict_first();
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;  // stages per 64-row tile
         uint32_t stage = 0, phase = 0, sslot = 0, sphase = 0;
         while (true) {
@@ -190,8 +206,11 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             }
             if (it < 0) break;
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+            const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
             const int row0 = w0.x, nrows = w0.y;
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
+            uint64_t policy = pol_normal;
+            if ((flags & SCAN_FLAG_L2_SIBLINGS) && w1.w > 1) policy = (w1.z + 1 == w1.w) ? pol_drop : pol_keep;
             for (int t = 0; t < ntiles; ++t) {
                 for (int s = 0; s < SPT; ++s) {
                     const int kb0 = s * SCAN_BOXES;
@@ -199,11 +218,11 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
                     if (ptx::elect_one()) {
                         uint8_t* dst = stages + (size_t)stage * SCAN_STAGE_BYTES;
-                        if (dbg & 1) {  // ablation: no loads, the MMAs run on whatever the stage holds
+                        if (LMI_DBG(dbg & 1)) {  // ablation: no loads, the MMAs run on whatever the stage holds
                             ptx::mbar_arrive(&bars->full[stage]);
                             nb = 0;
                         } else {
-                            if (dbg & 4) nb = (nb + 1) / 2;  // ablation: half the operand traffic (stale boxes for the rest)
+                            if (LMI_DBG(dbg & 4)) nb = (nb + 1) / 2;  // ablation: half the operand traffic
                             ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
                         }
                         for (int b = 0; b < nb; ++b)
@@ -241,10 +260,17 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 }
         };
         if (mw == 1) skip_tile_stages();
+#ifdef LMI_PROFILE
         const bool prof = (dbg & 8) != 0 && mw == 0;
         long long p_sched = 0, p_q = 0, p_acc = 0, p_full = 0, p_issue = 0, p_n = 0, p_t0 = clock64(), p_c;
 #define PROF_BEGIN() if (prof) p_c = clock64()
 #define PROF_END(acc) if (prof) acc += clock64() - p_c
+#define PROF_COUNT() ++p_n
+#else
+#define PROF_BEGIN()
+#define PROF_END(acc)
+#define PROF_COUNT()
+#endif
         while (true) {
             PROF_BEGIN();
             const int it = next_item(sslot, sphase);
@@ -274,7 +300,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     PROF_END(p_full);
                     ptx::tc_fence_after();
                     PROF_BEGIN();
-                    ++p_n;
+                    PROF_COUNT();
                     if (ptx::elect_one()) {
                         // The descriptor's start-address field counts 16-byte units in its low word,
                         // so stage / box / k offsets are plain adds on that word.  A full stage is
@@ -317,12 +343,15 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 skip_tile_stages();  // the other issuer's tile
             }
         }
+#ifdef LMI_PROFILE
         if (prof && lane == 0 && blockIdx.x < 148) {
             long long* o = g_scan_prof + blockIdx.x * 8;
             o[0] = clock64() - p_t0; o[1] = p_sched; o[2] = p_q; o[3] = p_acc; o[4] = p_full; o[5] = p_issue; o[6] = p_n;
         }
+#endif
 #undef PROF_BEGIN
 #undef PROF_END
+#undef PROF_COUNT
     } else {
         // ===================== epilogue warps (thread == query row) =====================
         // 8 warps: warp w reads TMEM lanes [32*(w&3), +32) (the hardware's lane quarter of warp
@@ -419,7 +448,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     g[gi] = m;
                 }
                 const float mall = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
-                if ((dbg & 2) == 0 && __any_sync(0xffffffffu, mall > tau)) {
+                if (!LMI_DBG(dbg & 2) && __any_sync(0xffffffffu, mall > tau)) {
 #pragma unroll
                     for (int gi = 0; gi < 4; ++gi) {
                         if (__any_sync(0xffffffffu, g[gi] > tau)) {
@@ -521,9 +550,11 @@ static EncodeTiledFn get_encode_fn() {
 
 }  // namespace lmi
 
+#ifdef LMI_PROFILE
 extern "C" int lmi_debug_scan_profile(long long* host_out /* [148*8] */) {
     return (int)cudaMemcpyFromSymbol(host_out, lmi::g_scan_prof, sizeof(long long) * 148 * 8);
 }
+#endif
 
 extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int nq, int B,
                              const int32_t* pair_list, const int32_t* items, const int32_t* n_items,
@@ -538,6 +569,8 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
 
+    const int flags = impl >> 8;
+    impl &= 0xff;
     if (impl == 1) {
         const int grid = (int)(max_items < (int64_t)sms * 8 ? max_items : (int64_t)sms * 8);
         lmi::scan_topk_simt_kernel<<<grid, lmi::SCAN_M, (size_t)d * sizeof(__half), st>>>(
@@ -561,19 +594,24 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return LMI_E_DRIVER;
 
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in to > 48 KB of dynamic shared memory is per device (context): remember it per device id
+    static bool attr_set[64] = {};
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(lmi::scan_topk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)lmi::SCAN_SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int grid = (int)(max_items < (int64_t)sms ? max_items : (int64_t)sms);
+    int dbg = 0;
+#ifdef LMI_PROFILE
     const char* dbg_env = getenv("LMI_SCAN_ABLATE");  // profiling ablations only; results are wrong when set
-    const int dbg = dbg_env ? atoi(dbg_env) : 0;
+    dbg = dbg_env ? atoi(dbg_env) : 0;
+#endif
     cudaError_t me = cudaMemsetAsync(const_cast<int32_t*>(n_items) + 1, 0, sizeof(int32_t), st);  // scheduler counter
     if (me != cudaSuccess) return (int)me;
     lmi::scan_topk_tc_kernel<<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
-        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row, dbg);
+        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row, flags,
+        dbg);
     return static_cast<int>(cudaGetLastError());
 }

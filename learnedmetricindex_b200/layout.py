@@ -36,7 +36,7 @@ def padded_dim(d: int) -> int:
 
 class DeviceBucketLayout:
     def __init__(self, vectors: torch.Tensor, bucket_off: torch.Tensor, ids: torch.Tensor, bucket_paths=None,
-                 d_data: Optional[int] = None):
+                 d_data: Optional[int] = None, inexact_values: int = 0):
         assert vectors.is_cuda and vectors.dtype == torch.float16 and vectors.is_contiguous()
         assert bucket_off.dtype == torch.int64 and ids.dtype == torch.int32
         self.vectors = vectors
@@ -48,6 +48,9 @@ class DeviceBucketLayout:
         self.n_buckets = self.bucket_off_host.shape[0] - 1
         sizes = np.diff(self.bucket_off_host)
         self.max_bucket = int(sizes.max()) if sizes.size else 0
+        self.n_nonempty = int((sizes > 0).sum())  # buckets holding rows HERE (a shard owns only some)
+        # values the f32 -> fp16 conversion changed while this layout was built (0 for fp16 sources)
+        self.inexact_values = int(inexact_values)
         self.bucket_paths = bucket_paths  # multi-level: bucket id -> path tuple
         self.device = vectors.device
 
@@ -56,21 +59,25 @@ class DeviceBucketLayout:
     def from_device(cls, x: torch.Tensor, labels: torch.Tensor, n_buckets: int,
                     ids: Optional[torch.Tensor] = None, chunk: int = 1 << 20, bucket_paths=None,
                     free_input: bool = False) -> "DeviceBucketLayout":
-        """``x`` (fp16/f32 [n,d]) and bucket ids ``labels`` (int64[n], -1 = drop) already on the GPU."""
+        """``x`` (fp16/f32 [n,d]) and bucket ids ``labels`` (int64[n]) already on the GPU.  A row whose
+        label is negative has no bucket and is dropped (the reference keeps such rows under an
+        ``EMPTY_VALUE`` path that no query can reach, LearnedIndexBuilder.py:67-76)."""
         L = _native.lib()
         dev = x.device
         n, d = x.shape
         labels = labels.to(dev, torch.int64).reshape(-1)
         assert labels.shape[0] == n
+        assert int(labels.max().item()) < n_buckets if n else True, "bucket label out of range"
         keep = labels >= 0
         counts = torch.bincount(labels[keep], minlength=n_buckets)[:n_buckets]
         off = torch.zeros(n_buckets + 1, dtype=torch.int64, device=dev)
         off[1:] = torch.cumsum(counts, 0)
         n_kept = int(off[-1].item())
-        # stable sort by bucket -> destination row of every source row
+        # stable sort by bucket -> destination row of every source row (dropped rows sort last: dest -1)
         order = torch.sort(torch.where(keep, labels, torch.full_like(labels, n_buckets)), stable=True).indices
         dest = torch.empty(n, dtype=torch.int64, device=dev)
         dest[order] = torch.arange(n, dtype=torch.int64, device=dev)
+        dest = torch.where(keep, dest, torch.full_like(dest, -1))
         if ids is None:
             ids = torch.arange(1, n + 1, dtype=torch.int64, device=dev)
         ids_sorted = ids.to(dev, torch.int64)[order][:n_kept]
@@ -79,17 +86,17 @@ class DeviceBucketLayout:
         del order
         ld = padded_dim(d)
         out = torch.empty((max(n_kept, 1), ld), dtype=torch.float16, device=dev)
-        if n_kept < n:
-            # dropped rows scatter past the end: give them a scratch destination inside bounds
-            raise NotImplementedError("rows without a bucket are not supported")
+        inexact = torch.zeros(1, dtype=torch.int64, device=dev)
         x = x.contiguous()
         for s in range(0, n, chunk):
             m = min(chunk, n - s)
             _native.check(L.lmi_scatter_rows(x[s : s + m].data_ptr(), int(x.dtype == torch.float16),
-                                             dest[s : s + m].data_ptr(), m, d, out.data_ptr(), ld, _stream_ptr()),
+                                             dest[s : s + m].data_ptr(), m, d, out.data_ptr(), ld,
+                                             inexact.data_ptr(), _stream_ptr()),
                           "lmi_scatter_rows")
         torch.cuda.current_stream().synchronize()
-        return cls(out[:n_kept] if n_kept else out[:0], off, ids32, bucket_paths, d_data=d)
+        return cls(out[:n_kept] if n_kept else out[:0], off, ids32, bucket_paths, d_data=d,
+                   inexact_values=int(inexact.item()))
 
     @classmethod
     def from_host(cls, data_search, labels: np.ndarray, n_buckets: int, ids: Optional[np.ndarray] = None,
@@ -122,6 +129,7 @@ class DeviceBucketLayout:
         ids32 = torch.from_numpy((ids[order] & 0xFFFFFFFF).astype(np.uint32).view(np.int32).copy()).to(dev)
         ld = padded_dim(d)
         out = torch.empty((max(n, 1), ld), dtype=torch.float16, device=dev)
+        inexact = torch.zeros(1, dtype=torch.int64, device=dev)
         is_f16 = mat.dtype == np.float16
         if mat.dtype not in (np.float16, np.float32):
             mat = mat.astype(np.float32)
@@ -130,9 +138,9 @@ class DeviceBucketLayout:
             blk = torch.from_numpy(np.ascontiguousarray(mat[s : s + m])).to(dev)
             dst = torch.from_numpy(dest[s : s + m]).to(dev)
             _native.check(L.lmi_scatter_rows(blk.data_ptr(), int(is_f16), dst.data_ptr(), m, d, out.data_ptr(),
-                                             ld, _stream_ptr()), "lmi_scatter_rows")
+                                             ld, inexact.data_ptr(), _stream_ptr()), "lmi_scatter_rows")
             torch.cuda.current_stream().synchronize()
-        return cls(out[:n], torch.from_numpy(off), ids32, bucket_paths, d_data=d)
+        return cls(out[:n], torch.from_numpy(off), ids32, bucket_paths, d_data=d, inexact_values=int(inexact.item()))
 
     # ------------------------------------------------------------------------------
     def restrict_to_buckets(self, mine: Sequence[int]) -> "DeviceBucketLayout":
@@ -150,7 +158,7 @@ class DeviceBucketLayout:
         if vec.shape[0] == 0:
             vec = torch.zeros((1, self.d), dtype=torch.float16, device=self.device)[:0]
         return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths,
-                                  d_data=self.d_data)
+                                  d_data=self.d_data, inexact_values=self.inexact_values)
 
     def restrict_to_slice(self, rank: int, world: int) -> "DeviceBucketLayout":
         """Shard: keep rows ``[s_b*rank//world, s_b*(rank+1)//world)`` of EVERY bucket -- every rank
@@ -169,4 +177,4 @@ class DeviceBucketLayout:
         vec = self.vectors[sel].contiguous() if sel.numel() else \
             torch.zeros((1, self.d), dtype=torch.float16, device=self.device)[:0]
         return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths,
-                                  d_data=self.d_data)
+                                  d_data=self.d_data, inexact_values=self.inexact_values)

@@ -76,6 +76,11 @@ class NeuralNetwork:
         self.impl = os.environ.get("LMI_MLP_IMPL", "tc")
         self._w_parts: Optional[List[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]] = None
 
+    @property
+    def launches_per_topn(self) -> int:
+        """Kernel launches of one ``topn_device`` call (input split + one per layer + softmax/top-n)."""
+        return (1 if self._tc_ok() else 0) + len(self.layers) + 1
+
     # -- construction from the reference's objects ------------------------------------
     @classmethod
     def from_reference(cls, nn, device=None) -> "NeuralNetwork":

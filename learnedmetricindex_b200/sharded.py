@@ -92,7 +92,7 @@ class PeerBuffers:
     all-gather and k-way merge in one launch.  Two blocks alternate so a rank may start the next
     search while slower peers still read its previous results (one barrier per search)."""
 
-    def __init__(self, nq: int, k: int, world: int, rank: int, device, group=None):
+    def __init__(self, nq: int, k: int, world: int, rank: int, device, group=None, n_blocks: int = 2):
         import torch.distributed._symmetric_memory as symm_mem
 
         self.nq, self.k, self.world, self.rank = nq, k, world, rank
@@ -100,7 +100,7 @@ class PeerBuffers:
         self.bytes_i = nq * k * 4
         self.per_rank = -(-(self.bytes_d + self.bytes_i) // 16) * 16
         self.blocks, self.handles = [], []
-        for _ in range(2):
+        for _ in range(n_blocks):  # a captured graph owns ONE block (fixed pointers); two graphs alternate instead
             t = symm_mem.empty(self.per_rank, dtype=torch.uint8, device=device)
             t.zero_()
             self.handles.append(symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD))
@@ -113,19 +113,22 @@ class PeerBuffers:
         i = blk[self.bytes_d : self.bytes_d + self.bytes_i].view(torch.int32).view(self.nq, self.k)
         return d, i
 
-    def exchange_and_merge(self):
+    def exchange_and_merge(self, out=None):
         from . import _native
 
         hdl = self.handles[self.turn]
         dev = self.blocks[0].device
-        out_d = torch.empty((self.nq, self.k), dtype=torch.float64, device=dev)
-        out_i = torch.empty((self.nq, self.k), dtype=torch.int32, device=dev)
+        if out is not None:
+            out_d, out_i = out
+        else:
+            out_d = torch.empty((self.nq, self.k), dtype=torch.float64, device=dev)
+            out_i = torch.empty((self.nq, self.k), dtype=torch.int32, device=dev)
         hdl.barrier(channel=0)  # every rank's block of this turn is written (device-side, on this stream)
         _native.check(_native.lib().lmi_merge_ranks_peer(hdl.buffer_ptrs_dev, self.bytes_d, self.world, self.nq,
                                                          self.k, out_d.data_ptr(), out_i.data_ptr(),
                                                          torch.cuda.current_stream().cuda_stream),
                       "lmi_merge_ranks_peer")
-        self.turn ^= 1
+        self.turn = (self.turn + 1) % len(self.blocks)
         return out_d, out_i
 
 
@@ -135,13 +138,14 @@ class PeerGather:
     step, one kernel copies every peer's block over NVLink.  Two blocks alternate (see
     ``PeerBuffers``)."""
 
-    def __init__(self, bytes_per_rank: int, world: int, device, group=None):
+    def __init__(self, bytes_per_rank: int, world: int, device, group=None, n_blocks: int = 2):
         import torch.distributed._symmetric_memory as symm_mem
 
         self.bytes = -(-max(bytes_per_rank, 16) // 16) * 16
         self.world = world
         self.blocks, self.handles = [], []
-        for _ in range(2):
+        self.recv = None  # n_blocks == 1 (graph capture): ONE receive buffer with a fixed address
+        for _ in range(n_blocks):
             t = symm_mem.empty(self.bytes, dtype=torch.uint8, device=device)
             t.zero_()
             self.handles.append(symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD))
@@ -156,11 +160,16 @@ class PeerGather:
         from . import _native
 
         hdl = self.handles[self.turn]
-        recv = torch.empty(self.world * self.bytes, dtype=torch.uint8, device=self.blocks[0].device)
+        if len(self.blocks) == 1:
+            if self.recv is None:
+                self.recv = torch.empty(self.world * self.bytes, dtype=torch.uint8, device=self.blocks[0].device)
+            recv = self.recv
+        else:
+            recv = torch.empty(self.world * self.bytes, dtype=torch.uint8, device=self.blocks[0].device)
         hdl.barrier(channel=0)
         _native.check(_native.lib().lmi_gather_peer(hdl.buffer_ptrs_dev, self.bytes, self.world, recv.data_ptr(),
                                                     torch.cuda.current_stream().cuda_stream), "lmi_gather_peer")
-        self.turn ^= 1
+        self.turn = (self.turn + 1) % len(self.blocks)
         return recv
 
 
@@ -226,21 +235,41 @@ class ShardedLearnedIndex:
         # "nccl": all-gather + lmi_merge_ranks (GatherBuffers; also what the gloo tests run)
         self.exchange = exchange or os.environ.get("LMI_EXCHANGE", "peer")
         self._bufs = {}
+        self._graphs = {}
         if self.exchange == "peer" and self.world > 1 and torch.device(local.device).type == "cuda":
-            # symmetric memory needs P2P mappings between all GPUs of the group: probe once and let every
-            # rank agree on the outcome (a rank that cannot map its peers must not leave the others waiting)
-            ok = 1
-            try:
-                import torch.distributed._symmetric_memory as symm_mem
+            self.exchange = "peer" if self._agree_on_peer_memory(local.device, group) else "nccl"
 
-                t = symm_mem.empty(16, dtype=torch.uint8, device=local.device)
-                symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD)
-            except Exception:  # noqa: BLE001 -- any failure means "use the collective library"
-                ok = 0
-            flag = torch.tensor([ok], dtype=torch.int32, device=local.device)
+    def _agree_on_peer_memory(self, device, group) -> bool:
+        """Symmetric memory needs P2P mappings between all GPUs of the group.  ``rendezvous`` is itself a
+        collective, so the ranks agree in TWO steps: first every rank tests what it can test alone (the
+        module imports, an allocation succeeds, every peer GPU is P2P-reachable) and the flags are
+        MIN-reduced -- only if all say yes does anybody enter ``rendezvous`` -- then the outcome of the
+        rendezvous is MIN-reduced as well.  A rank that cannot take part therefore never leaves the
+        others waiting inside a collective; all of them fall back to the NCCL exchange together."""
+        def agree(ok: bool) -> bool:
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
-            if int(flag.item()) == 0:
-                self.exchange = "nccl"
+            return bool(flag.item())
+
+        t = None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            me = torch.device(device).index
+            me = torch.cuda.current_device() if me is None else me
+            ok = all(torch.cuda.can_device_access_peer(me, o) for o in range(torch.cuda.device_count()) if o != me) \
+                if torch.cuda.device_count() >= self.world else True  # ranks on other devices than the visible ones
+            t = symm_mem.empty(16, dtype=torch.uint8, device=device) if ok else None
+        except Exception:  # noqa: BLE001 -- any failure means "use the collective library"
+            ok = False
+        if not agree(ok):
+            return False
+        try:
+            symm_mem.rendezvous(t, group if group is not None else dist.group.WORLD)
+            ok = True
+        except Exception:  # noqa: BLE001
+            ok = False
+        return agree(ok)
 
     def _buffers(self, nq: int, k: int, device):
         key = (nq, k)
@@ -272,6 +301,105 @@ class ShardedLearnedIndex:
         if isinstance(buf, PeerBuffers):
             return buf.exchange_and_merge()
         return gather_and_merge(buf, self.group)
+
+    # ------------------------------------------------------------------ CUDA graph ----------------
+    def search_graphed(self, qn, qs, n_categories, n_buckets: int, k: int):
+        """The whole sharded search as ONE graph replay per call (peer-memory exchange only): query upload
+        gather -> navigation of this rank's query slice -> bucket-order gather -> inversion / scan / merge of
+        the local buckets -> device-side barrier -> rank merge reading the peers' blocks.  Host inputs: only
+        this rank's 1/world slice crosses PCIe (copied into the graph's symmetric send block before the
+        replay), the rest arrives over NVLink inside the graph.  Every (shape, budget) owns TWO captured
+        instances that alternate, each with its own symmetric blocks: an instance's blocks are rewritten
+        two searches later, when every peer has passed the barrier in between (same argument as the
+        double-buffered eager path).  Returns ``(dists, nns, events)`` (static tensors of the instance)."""
+        from .LearnedIndex import PER_BUCKET_K
+        from .model import to_device_matrix
+
+        assert self.exchange == "peer" and self.world > 1
+        shared = qs is qn
+        nq = len(qs)
+        dev = self.local.device
+        host_in = not (isinstance(qn, torch.Tensor) and qn.is_cuda)
+        dt = lambda x: (x.dtype if isinstance(x, torch.Tensor) else
+                        (torch.float16 if np.asarray(x).dtype == np.float16 else torch.float32))
+        if not host_in:  # device matrices are read in place: the graph is keyed on their addresses
+            assert qn.is_contiguous() and qs.is_contiguous()
+        key = (nq, tuple(np.shape(qn)), dt(qn), tuple(np.shape(qs)), dt(qs), shared, host_in, tuple(n_categories),
+               int(n_buckets), int(k), 0 if host_in else qn.data_ptr(), 0 if host_in else qs.data_ptr())
+        entry = self._graphs.get(key)
+        if entry is None:
+            entry = dict(instances=[None, None], turn=0)
+            self._graphs[key] = entry
+        t = entry["turn"]
+        entry["turn"] ^= 1
+        inst = entry["instances"][t]
+        start, stop, per = query_slice(nq, self.world, self.rank)
+        k_out = PER_BUCKET_K if int(n_buckets) == 1 else int(k)
+
+        def upload(inst):
+            """Stage this call's queries where the graph reads them."""
+            for name, src in (("n", qn),) + ((("s", qs),) if not shared else ()):
+                if host_in:  # H2D of the 1/world slice only, straight into the symmetric send block
+                    part = src[start:stop]
+                    if not isinstance(part, torch.Tensor):
+                        part = torch.from_numpy(np.ascontiguousarray(part))
+                    dst = inst["send_" + name]
+                    dst[: part.shape[0]].copy_(part.to(dst.dtype), non_blocking=True)
+                # device inputs are read in place (see the key)
+
+        if inst is None:
+            inst = {}
+            dtypes = {"n": dt(qn), "s": dt(qs)}
+            shapes = {"n": tuple(np.shape(qn)), "s": tuple(np.shape(qs))}
+            for name in ("n",) + (("s",) if not shared else ()):
+                if host_in:
+                    row_bytes = shapes[name][1] * torch.empty(0, dtype=dtypes[name]).element_size()
+                    pg = PeerGather(per * row_bytes, self.world, dev, self.group, n_blocks=1)
+                    inst["pg_" + name] = pg
+                    inst["send_" + name] = pg.send_block()[: per * row_bytes].view(dtypes[name]).view(per, shapes[name][1])
+                else:
+                    inst["full_" + name] = qn if name == "n" else qs
+            inst["pg_order"] = PeerGather(per * int(n_buckets) * 4, self.world, dev, self.group, n_blocks=1)
+            inst["res"] = PeerBuffers(nq, k_out, self.world, self.rank, dev, self.group, n_blocks=1)
+            inst["out"] = (torch.empty((nq, k_out), dtype=torch.float64, device=dev),
+                           torch.empty((nq, k_out), dtype=torch.int32, device=dev))
+
+            def body(events):
+                full = {}
+                for name in ("n",) + (("s",) if not shared else ()):
+                    if host_in:
+                        pg = inst["pg_" + name]
+                        rb = inst["send_" + name].shape[1] * inst["send_" + name].element_size()
+                        raw = pg.gather().view(self.world, pg.bytes)[:, : per * rb]
+                        full[name] = raw.reshape(-1).view(dtypes[name]).view(self.world * per, shapes[name][1])[:nq]
+                    else:
+                        full[name] = inst["full_" + name]
+                fn = full["n"]
+                fs = fn if shared else full["s"]
+                if events is not None:
+                    events[0].record()
+                local_order, _ = self.local._bucket_order_device(fn[start:stop], int(n_buckets), list(n_categories))
+                pg = inst["pg_order"]
+                blk = pg.send_block()[: per * int(n_buckets) * 4].view(torch.int32).view(per, int(n_buckets))
+                blk[: local_order.shape[0]].copy_(local_order)
+                order = pg.gather().view(self.world, pg.bytes)[:, : per * int(n_buckets) * 4].reshape(-1) \
+                    .view(torch.int32).view(self.world * per, int(n_buckets))[:nq]
+                self.local.search_device(fn, fs, n_categories, n_buckets, k, events=events,
+                                         out=inst["res"].local_views(), bucket_order=order.contiguous())
+                inst["res"].exchange_and_merge(out=inst["out"])
+
+            upload(inst)
+            body(None)  # eager run: every rank executes the same barriers, lazy caches fill outside the capture
+            torch.cuda.current_stream().synchronize()
+            inst["events"] = [torch.cuda.Event(enable_timing=True, external=True) for _ in range(5)]
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                body(inst["events"])
+            inst["graph"] = graph
+            entry["instances"][t] = inst
+        upload(inst)
+        inst["graph"].replay()
+        return inst["out"][0], inst["out"][1], inst["events"]
 
     def _gather_rows_peer(self, part: torch.Tensor, n_rows: int) -> torch.Tensor:
         """All-gather of row blocks over peer memory: ``part`` holds this rank's rows
@@ -316,11 +444,22 @@ class ShardedLearnedIndex:
 
         t0 = time.time()
         dev = self.local.device
-        qn = self._upload_sharded(queries_navigation, dev)
-        qs = qn if queries_search is queries_navigation else self._upload_sharded(queries_search, dev)
-        d, i = self.search_device(qn, qs, list(n_categories), n_buckets, k)
-        dists = d.cpu().numpy()
-        nns = i.cpu().numpy().view(np.uint32)
         times = defaultdict(float)
+        if (self.exchange == "peer" and self.world > 1 and torch.device(dev).type == "cuda" and self.local.use_graphs
+                and self.shard_navigation and len(queries_search) >= self.world):
+            d, i, ev = self.search_graphed(queries_navigation,
+                                           queries_navigation if queries_search is queries_navigation else queries_search,
+                                           list(n_categories), n_buckets, k)
+            dists = d.cpu().numpy()
+            nns = i.cpu().numpy().view(np.uint32)
+            stage = [ev[j].elapsed_time(ev[j + 1]) / 1e3 for j in range(4)]
+            times.update(inference=stage[0], search_within_buckets=stage[1] + stage[2] + stage[3],
+                         seq_search=stage[2], sort=stage[3])
+        else:
+            qn = self._upload_sharded(queries_navigation, dev)
+            qs = qn if queries_search is queries_navigation else self._upload_sharded(queries_search, dev)
+            d, i = self.search_device(qn, qs, list(n_categories), n_buckets, k)
+            dists = d.cpu().numpy()
+            nns = i.cpu().numpy().view(np.uint32)
         times["search"] = time.time() - t0
         return dists, nns, times

@@ -70,9 +70,15 @@ def make_vectors(
 def _kmeans_centroids(x: torch.Tensor, k: int, iters: int, g: torch.Generator) -> torch.Tensor:
     idx = torch.randperm(x.shape[0], generator=g, device=x.device)[:k]
     c = x[idx].clone()
+    rows = torch.arange(x.shape[0], device=x.device)
     for _ in range(iters):
         lab = (x @ c.t()).argmax(dim=1)  # unit vectors: max inner product == nearest
-        sums = torch.zeros_like(c).index_add_(0, lab, x)
+        # segment sums as a one-hot GEMM: bit-reproducible run to run (index_add_ adds with float
+        # atomics on CUDA, which made the stand-in index -- bucket sizes, recall -- differ between runs)
+        onehot = torch.zeros((k, x.shape[0]), dtype=x.dtype, device=x.device)
+        onehot[lab, rows] = 1
+        sums = onehot @ x
+        del onehot
         cnt = torch.bincount(lab, minlength=k).to(x.dtype).unsqueeze(1)
         c = torch.where(cnt > 0, torch.nn.functional.normalize(sums / cnt.clamp(min=1), dim=1), c)
     return c

@@ -1,8 +1,10 @@
 """Run the UNMODIFIED reference ``li`` package in-process (TEST INFRASTRUCTURE).
 
-Only usable where ``/root/reference`` exists (the build container).  Nothing
-that runs on the GPU box (``-m gpu`` tests, ``smoke()``, ``bench.py``) may call
-this; those use ``oracle.lmi_oracle`` and the committed ``tests/golden``.
+Needs the reference package: ``/root/reference/search/li`` (the build container) or its
+byte-identical staged copy ``oracle/_ref/li`` (``oracle/build_ref.py``; git-ignored, ships to
+the GPU box with the gpurun snapshot).  The ``-m gpu`` tests and ``smoke()`` never call this
+(they use ``oracle.lmi_oracle`` and the committed ``tests/golden``); ``bench.py --impl
+reference`` and its ``cpu_baseline`` leg do, to time the reference's own search on the host.
 
 Three shims are needed to execute the reference under this image:
 
@@ -23,12 +25,21 @@ import sys
 import numpy as np
 
 REFERENCE_ROOT = os.environ.get("LMI_REFERENCE_ROOT", "/root/reference")
-_SEARCH_DIR = os.path.join(REFERENCE_ROOT, "search")
-_SHIM_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "faiss_shim")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SEARCH_DIRS = (os.path.join(REFERENCE_ROOT, "search"), os.path.join(_HERE, "_ref"))
+_SHIM_DIR = os.path.join(_HERE, "faiss_shim")
+
+
+def reference_dir():
+    """Directory holding the reference's ``li`` package: the checkout, else the staged copy."""
+    for d in _SEARCH_DIRS:
+        if os.path.isfile(os.path.join(d, "li", "LearnedIndex.py")):
+            return d
+    return None
 
 
 def reference_available() -> bool:
-    return os.path.isfile(os.path.join(_SEARCH_DIR, "li", "LearnedIndex.py"))
+    return reference_dir() is not None
 
 
 class _ListOgrid:
@@ -49,12 +60,14 @@ def import_reference():
     """Returns the reference modules as a dict; idempotent."""
     if _imported:
         return _imported
-    if not reference_available():
-        raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
+    search_dir = reference_dir()
+    if search_dir is None:
+        raise RuntimeError(f"reference not found under {REFERENCE_ROOT} nor staged under oracle/_ref "
+                           "(python -m oracle.build_ref)")
     if _SHIM_DIR not in sys.path:
         sys.path.insert(0, _SHIM_DIR)
-    if _SEARCH_DIR not in sys.path:
-        sys.path.insert(0, _SEARCH_DIR)
+    if search_dir not in sys.path:
+        sys.path.insert(0, search_dir)
     if not isinstance(np.ogrid, _ListOgrid):
         np.ogrid = _ListOgrid(np.ogrid)
     import li.LearnedIndex as m_index  # noqa: E402
@@ -64,7 +77,7 @@ def import_reference():
 
     # the per-bucket tqdm bar (LearnedIndex.py:350) is noise in test logs
     m_index.tqdm = lambda it, *a, **k: it
-    _imported.update(index=m_index, model=m_model, pq=m_pq, utils=m_utils)
+    _imported.update(index=m_index, model=m_model, pq=m_pq, utils=m_utils, source=search_dir)
     return _imported
 
 
@@ -115,20 +128,23 @@ def make_reference_index(root_layers, root_type, internal=None, bucket_paths=Non
 
 def run_reference_search(
     li, data_nav, queries_nav, data_search, queries_search, data_prediction,
-    n_categories, n_buckets, k=10, ids=None,
+    n_categories, n_buckets, k=10, ids=None, copy=None,
 ):
     """Calls the reference ``LearnedIndex.search`` (LearnedIndex.py:41-161).
 
     ``data_nav`` / ``data_search`` are ndarrays; they are wrapped in two distinct
     DataFrames whose index is ``ids`` (default 1..n, as search/search.py:190-191).
+    ``copy=False`` lets both frames view the caller's array (needed at 10M rows, where a
+    second and third f32 copy would not fit in RAM); the reference only ADDS and DROPS label
+    columns on ``data_navigation`` (:101-104, :153-157), it never writes into the vectors.
     """
     import pandas as pd
 
     n = data_nav.shape[0]
     if ids is None:
         ids = np.arange(1, n + 1)
-    df_nav = pd.DataFrame(np.asarray(data_nav), index=pd.Index(ids))
-    df_search = pd.DataFrame(np.asarray(data_search), index=pd.Index(ids))
+    df_nav = pd.DataFrame(np.asarray(data_nav), index=pd.Index(ids), copy=copy)
+    df_search = pd.DataFrame(np.asarray(data_search), index=pd.Index(ids), copy=copy)
     dists, nns, times = li.search(
         data_navigation=df_nav,
         queries_navigation=queries_nav,

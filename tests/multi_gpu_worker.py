@@ -40,7 +40,11 @@ def main():
             for rep in range(3):  # repeated: the peer path alternates between its two blocks
                 d, i = eng.search_device(Q, Q, [C], B, k)
                 assert torch.equal(d, exp_d) and torch.equal(i, exp_i), (exchange, B, k, rep, rank)
-            # host-facing API (queries uploaded 1/world per rank and all-gathered)
+            if exchange == "peer":  # the whole sharded search as one graph replay (two alternating instances)
+                for rep in range(3):
+                    dg, ig, _ = eng.search_graphed(Q, Q, [C], B, k)
+                    assert torch.equal(dg, exp_d) and torch.equal(ig, exp_i), ("graph", B, k, rep, rank)
+            # host-facing API (queries uploaded 1/world per rank and all-gathered; graph replay on the peer path)
             dh, ih, _ = eng.search(None, Q.cpu().numpy(), None, Q.cpu().numpy(), None, [C], n_buckets=B, k=k)
             assert np.array_equal(dh, exp_d.cpu().numpy()) and np.array_equal(ih.view(np.int32), exp_i.cpu().numpy())
     # a batch that does not divide by the number of ranks (padded navigation / upload slices)

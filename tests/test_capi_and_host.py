@@ -24,12 +24,18 @@ def test_library_builds_loads_and_exports_header_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/lmi_b200.h but not exported"
     assert set(declared) == set(_native.EXPORTED_SYMBOLS), "ctypes signatures out of sync with the header"
-    assert lib.lmi_version() == 3
+    assert lib.lmi_version() == 4
     assert lib.lmi_error_string(0) == b"success"
     assert b"bad argument" in lib.lmi_error_string(-1)
     # size helpers are pure host functions
     assert lib.lmi_max_items(10000, 4, 120, 5) >= 5 * (40000 // 128 + 120)
     assert lib.lmi_invert_workspace_ints(10000, 4, 120) % 120 == 0
+    import ctypes
+    offs = (ctypes.c_int64 * 12)()
+    total = lib.lmi_workspace_layout(10000, 4, 120, 5, 768, offs)
+    assert total == offs[11] == lib.lmi_workspace_bytes(10000, 4, 120, 5) + 2 * 10000 * 768
+    assert all(offs[i] % 256 == 0 and offs[i] <= offs[i + 1] for i in range(11))
+    assert offs[9] - offs[8] >= 4 * 40000 * 10 * 10  # part_sim: P * 2*rmax * 10 floats
 
 
 def test_sass_is_blackwell_native():
@@ -88,11 +94,18 @@ def test_plan_scan(nq, B, C, n, maxb):
     from learnedmetricindex_b200 import plan_scan
     from learnedmetricindex_b200.LearnedIndex import MAX_RANGES
 
-    length, rmax = plan_scan(nq, B, C, n, maxb)
-    assert length % 64 == 0 and length >= 64
-    assert 1 <= rmax <= MAX_RANGES
-    assert rmax * length >= maxb  # every bucket is covered
-    assert (rmax - 1) * length < maxb or rmax == 1
+    for nonempty in (None, max(1, C // 8)):
+        p = plan_scan(nq, B, C, n, maxb, n_nonempty=nonempty)
+        length, tail, rmax = p["range_len"], p["tail_range_len"], p["rmax"]
+        assert length % 64 == 0 and length >= 64
+        assert 1 <= rmax <= MAX_RANGES
+        shortest = tail or length
+        assert tail % 64 == 0 and tail < length and 0 <= p["tail_permille"] <= 400
+        assert (tail == 0) == (p["tail_permille"] == 0)
+        assert rmax * shortest >= maxb  # every bucket is covered whichever length cuts it
+        assert (rmax - 1) * shortest < maxb or rmax == 1
+        if tail:
+            assert -(-maxb // tail) <= 16  # <= 32 partial lists per probe: the merge's one-list-per-lane path
 
 
 def test_flat_bucket_ids_follow_groupby_key_order():

@@ -85,14 +85,16 @@ def test_invert_matches_numpy():
 
     L = _native.lib()
     rs = np.random.RandomState(5)
-    for nq, B, C, rng_len in [(1, 1, 7, 64), (37, 3, 11, 128), (5000, 4, 120, 1024), (20000, 16, 50, 4096)]:
+    cases = [(1, 1, 7, 64, 0, 0), (37, 3, 11, 128, 0, 0), (5000, 4, 120, 1024, 0, 0), (20000, 16, 50, 4096, 0, 0),
+             (5000, 4, 120, 1024, 256, 300), (3000, 7, 1500, 2048, 512, 150)]  # last two: two-level cut, C > 1024
+    for nq, B, C, rng_len, tail_len, tail_pm in cases:
         order = np.stack([rs.permutation(C)[:B] for _ in range(nq)]).astype(np.int32)
         order[rs.rand(nq, B) < 0.02] = -1  # ignored entries
         sizes = rs.randint(0, 3000, C)
-        sizes[rs.rand(C) < 0.1] = 0
+        sizes[rs.rand(C) < 0.1] = 0  # buckets without rows here (empty, or owned by another rank)
         off = np.zeros(C + 1, dtype=np.int64)
         off[1:] = np.cumsum(sizes)
-        rmax = max(1, int(-(-sizes.max() // rng_len)))
+        rmax = max(1, int(-(-sizes.max() // (tail_len or rng_len))))
         dev = torch.device("cuda")
         t = lambda a: torch.from_numpy(a).to(dev)
         P = nq * B
@@ -103,16 +105,16 @@ def test_invert_matches_numpy():
         d_pl = torch.full((P,), -7, dtype=torch.int32, device=dev)
         d_sop = torch.full((P,), -7, dtype=torch.int32, device=dev)
         d_items = torch.zeros(max_items * 8, dtype=torch.int32, device=dev)
-        d_n = torch.zeros(2, dtype=torch.int32, device=dev)
+        d_n = torch.full((2,), 5, dtype=torch.int32, device=dev)
         work = torch.empty(int(L.lmi_invert_workspace_ints(nq, B, C)), dtype=torch.int32, device=dev)
         d_order, d_boff = t(order), t(off)
-        _native.check(L.lmi_invert(d_order.data_ptr(), nq, B, C, d_boff.data_ptr(), rng_len, d_counts.data_ptr(),
-                                   d_off.data_ptr(), d_bl.data_ptr(), d_pl.data_ptr(), d_sop.data_ptr(),
-                                   d_items.data_ptr(),
-                                   d_n.data_ptr(), max_items, work.data_ptr(), 0))
+        _native.check(L.lmi_invert(d_order.data_ptr(), nq, B, C, d_boff.data_ptr(), rng_len, tail_len, tail_pm,
+                                   d_counts.data_ptr(), d_off.data_ptr(), d_bl.data_ptr(), d_pl.data_ptr(),
+                                   d_sop.data_ptr(), d_items.data_ptr(), d_n.data_ptr(), max_items, work.data_ptr(), 0))
         torch.cuda.synchronize()
         flat = order.reshape(-1)
-        valid = flat >= 0
+        # a probe counts when its bucket id is valid and the bucket holds rows in this layout
+        valid = (flat >= 0) & (sizes[np.clip(flat, 0, C - 1)] > 0)
         exp_counts = np.bincount(flat[valid], minlength=C)
         assert np.array_equal(d_counts.cpu().numpy(), exp_counts)
         exp_off = np.concatenate(([0], np.cumsum(exp_counts)))
@@ -123,24 +125,34 @@ def test_invert_matches_numpy():
         sop = d_sop.cpu().numpy()
         assert np.array_equal(sop[exp_pl], np.arange(valid.sum()))
         assert (sop[~valid] == -1).all()
-        # work items: every (bucket with m>0 and rows>0) x range x query tile exactly once
+        # work items: every (bucket with m>0 and rows>0) x range x query tile exactly once; buckets listed after
+        # (1000 - tail_pm)/1000 of the work (rows x query tiles, in bucket order) are cut with tail_len
         n_items = int(d_n[0].item())
+        assert int(d_n[1].item()) == 0  # the scan's item counter is reset
         items = d_items.cpu().numpy().reshape(-1, 8)[:n_items]
-        exp_items = []
+        tiles = -(-exp_counts // 128)
+        work_b = sizes.astype(np.int64) * tiles
+        before = np.concatenate(([0], np.cumsum(work_b)))[:-1]
+        two = tail_pm > 0 and 0 < tail_len < rng_len
+        tail_from = work_b.sum() // 1000 * (1000 - tail_pm) if two else work_b.sum() + 1
+        exp_items, exp_bl = [], np.zeros(C, dtype=np.int64)
         for b in range(C):
             m, s = exp_counts[b], sizes[b]
             if m == 0 or s == 0:
                 continue
-            nr = -(-s // rng_len)
+            rl = tail_len if before[b] >= tail_from else rng_len
+            nr = -(-s // rl)
             ln = -(-(-(-s // nr)) // 64) * 64  # equal ranges, rounded up to 64 rows
+            exp_bl[b] = 2 * nr
             for r in range(nr):
-                for tq in range(-(-m // 128)):
+                for tq in range(tiles[b]):
                     exp_items.append((off[b] + r * ln, min(ln, s - r * ln), exp_off[b] + tq * 128,
-                                      min(128, m - tq * 128), 2 * r, b, 0, 0))
-        exp_bl = np.where((exp_counts > 0) & (sizes > 0), 2 * -(-sizes // rng_len), 0)
+                                      min(128, m - tq * 128), 2 * r, b, tq, tiles[b]))
         assert np.array_equal(d_bl.cpu().numpy(), exp_bl)
         assert n_items == len(exp_items) <= max_items
         assert np.array_equal(items, np.array(exp_items, dtype=np.int32).reshape(-1, 8))
+        if two:
+            assert len({it[1] for it in exp_items}) > 1
 
 
 @pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
