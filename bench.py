@@ -164,10 +164,33 @@ def make_chunk(ci, m, spec, device):
     return syn.make_vectors(m, spec, device=device, stream=1000 + ci, chunk=CHUNK)
 
 
+STANDIN_ASSET = os.path.join(ROOT, "bench_assets", "standin_mlp4_768_120.npz")
+
+
+def load_standin_asset(spec, C, device):
+    """The committed stand-in weights (tools/make_standin_asset.py: trained once, on the CPU, from a draw of the
+    default mixture) when the workload is the default one -- so every run, box, --gpus N and arm searches the
+    SAME index; None otherwise."""
+    try:
+        z = np.load(STANDIN_ASSET)
+    except Exception:
+        return None
+    c, d, _, _, centres, latent = (int(v) for v in z["meta"])
+    if (c, d, centres, latent) != (C, D, spec.n_centres, spec.latent_dim) or abs(float(z["noise"]) - spec.noise) > 1e-12:
+        return None
+    return [(torch.from_numpy(z["W1"]).to(device), torch.from_numpy(z["b1"]).to(device)),
+            (torch.from_numpy(z["W2"]).to(device), torch.from_numpy(z["b2"]).to(device))]
+
+
 def train_index(spec, C, device, rank, world, steps):
-    """Stand-in for LearnedIndexBuilder.build on a fresh 200k-row draw: rank 0 trains, weights broadcast."""
+    """Stand-in for LearnedIndexBuilder.build: the committed weights for the default workload, else rank 0 trains
+    on a fresh 200k-row draw and the weights are broadcast."""
     from learnedmetricindex_b200 import synthetic as syn
 
+    layers = load_standin_asset(spec, C, device)
+    if layers is not None:
+        log(f"index stand-in: committed weights {os.path.relpath(STANDIN_ASSET, ROOT)}")
+        return layers
     shapes = syn.mlp_layer_shapes("MLP-4", D, C)
     if rank == 0:
         xt = syn.make_vectors(TRAIN_ROWS, spec, device=device, stream=2).float()

@@ -36,6 +36,7 @@ MAX_RANGES = 32  # row ranges a bucket is cut into at most (lmi_merge_topk: <= 2
 LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
 DEFAULT_RANGE_ROWS = 24576  # upper bound on the rows of a scan work item (see plan_scan; sustained 10M sweep: 8192 +5 %, 16384 0, 24576 -1.9 %, 32768 -1.0 %)
+DEFAULT_SCAN_IMPL = 0
 GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index (least recently used goes first)
 WS_CACHE = 8  # batch shapes whose workspace is kept
 WS_ARRAYS = 11  # LMI_WS_ARRAYS
@@ -118,7 +119,7 @@ class _BatchWorkspace:
 
 
 class LearnedIndex:
-    def __init__(self, root_model, internal_models=None, bucket_paths=None, scan_impl: int = 0,
+    def __init__(self, root_model, internal_models=None, bucket_paths=None, scan_impl: Optional[int] = None,
                  allow_fp16_rounding: Optional[bool] = None):
         self.root_model = NeuralNetwork.from_reference(root_model)
         """The root model of the index."""
@@ -126,7 +127,9 @@ class LearnedIndex:
         """Path -> internal model (multi-level indexes)."""
         self.bucket_paths = [tuple(p) for p in (bucket_paths or [])]
         """List of paths to the buckets."""
-        self.scan_impl = scan_impl  # 0: tcgen05/TMA kernel; 1: CUDA-core verification kernel (tests)
+        # lmi_scan_topk impl: 0 = tcgen05/TMA kernel, one CTA per work item; 2 = the same kernel over clusters of
+        # two CTAs that share bucket rows by TMA multicast; 1 = CUDA-core verification kernel (tests)
+        self.scan_impl = int(os.environ.get("LMI_SCAN_IMPL", DEFAULT_SCAN_IMPL)) if scan_impl is None else int(scan_impl)
         # The scan computes f32 arithmetic on fp16 values -- exactly the reference's arithmetic when the data is
         # fp16 on disk (SISAP `emb`).  f32 data that fp16 cannot represent is ROUNDED (2^-11 relative per
         # component): None = warn once, True = accept silently, False = refuse (ValueError).

@@ -493,6 +493,338 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same scan with the bucket rows shared between TWO CTAs (a thread-block cluster of 2 = the two SMs
+// of a TPC) by TMA MULTICAST.  The cluster draws PAIRS of consecutive work items; CTA `rank` of the pair
+// takes item 2p + rank.  Items of one (bucket, row range) -- one per tile of 128 probing queries -- are
+// adjacent in the list, so most pairs are two query tiles over the SAME rows ("shared" pair): each CTA then
+// issues the TMA loads of half of every pipeline stage's boxes with .multicast::cluster, the box lands in
+// BOTH CTAs' shared memory and completes bytes on both CTAs' full barriers -- the rows cross L2 -> SM once
+// for the two tiles instead of twice.  A pair of unrelated items (a bucket's odd last tile next to the
+// first tile of the following range) runs the two CTAs independently, exactly like the single-CTA kernel.
+// Everything per item -- query gather into TMEM, tcgen05.mma with A in TMEM, the fused top-10 epilogue,
+// the partial lists written -- is identical to scan_topk_tc_kernel, so results are bit-identical.
+//
+// Protocol.  One cluster barrier per pair (all warps of both CTAs): when it completes every MMA of the
+// previous pair has finished in both CTAs (the epilogue warps only arrive after draining the last
+// accumulator tile), so all pipeline stages of both CTAs are free, the pipeline restarts at stage 0 in
+// lock step, and the next pair index -- drawn by the leader CTA's producer lane from the global counter and
+// written into both CTAs' shared memory before it arrives -- is visible.  `empty` barriers count 2
+// arrivals: in a shared pair a stage of CTA x is written by both producers, so it is free when BOTH issuers
+// are done with their copy (each tcgen05.commit is multicast to the two CTAs' barriers); in an independent
+// pair the CTA's own issuer commits twice.  Stage parities are tracked per stage (a bit mask), because a
+// pair may leave the ring anywhere and the next one starts at stage 0 again.
+struct PairBarriers {
+    uint64_t full[SCAN_STAGES];
+    uint64_t empty[SCAN_STAGES];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint64_t q_ready;
+    int32_t sched_pair[2];  // pair index of cluster round r is sched_pair[r & 1]
+    uint32_t tmem_base;
+};
+static_assert(sizeof(PairBarriers) <= 512, "barrier block too large");
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(SCAN_THREADS, 1)
+scan_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __restrict__ Q,
+                      const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
+                      const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int lmax,
+                      float* __restrict__ part_sim, int32_t* __restrict__ part_row) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    PairBarriers* bars = reinterpret_cast<PairBarriers*>(stages + (size_t)SCAN_STAGES * SCAN_STAGE_BYTES);
+    float* gates = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // [2 halves][128 rows]
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int KB = d / SCAN_KBLK;
+    const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;  // stages per 64-row tile
+    int n_items = *n_items_ptr;
+    if ((int64_t)n_items > max_items) n_items = (int)max_items;
+    const int n_pairs = (n_items + 1) >> 1;
+    const uint32_t rank = ptx::cluster_ctarank();
+    int* sched_counter = const_cast<int*>(n_items_ptr) + 1;
+    const bool scheduler = rank == 0 && warp == TMA_WARP && lane == 0;  // draws the pair indices for the cluster
+    auto publish_pair = [&](int slot, int p) {
+        *reinterpret_cast<volatile int32_t*>(&bars->sched_pair[slot]) = p;
+        ptx::st_cluster_u32(ptx::mapa(ptx::smem_u32(&bars->sched_pair[slot]), 1), (uint32_t)p);
+    };
+
+    if (warp == TMA_WARP && lane == 0) {
+        ptx::tma_prefetch_desc(&tmap);
+        for (int s = 0; s < SCAN_STAGES; ++s) {
+            ptx::mbar_init(&bars->full[s], 1);
+            ptx::mbar_init(&bars->empty[s], 2);
+        }
+        for (int b = 0; b < 2; ++b) {
+            ptx::mbar_init(&bars->acc_full[b], 1);
+            ptx::mbar_init(&bars->acc_empty[b], SCAN_EPI_WARPS);
+        }
+        ptx::mbar_init(&bars->q_ready, SCAN_EPI_WARPS * 32);
+        ptx::fence_barrier_init();
+    }
+    if (warp == MMA_WARP) {
+        ptx::tmem_alloc(&bars->tmem_base, TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    ptx::cluster_sync();  // barrier inits of BOTH CTAs are in place before anything is multicast
+    ptx::tc_fence_after();
+    const uint32_t tmem = bars->tmem_base;
+    int next_p = 0;
+    if (scheduler) {
+        publish_pair(0, atomicAdd(sched_counter, 1));
+        next_p = atomicAdd(sched_counter, 1);
+    }
+    ptx::cluster_sync();
+
+    // per-role running state (identical bookkeeping in the producer and both issuers)
+    uint32_t use_bits = 0;      // bit s: parity of how often stage s has been used so far in this CTA
+    uint32_t tcount = 0;        // score tiles so far (accumulator buffer = tcount & 1)
+    uint32_t item_parity = 0;   // items this CTA has processed so far (q_ready phase)
+    const uint32_t mw = warp - MMA_WARP;
+
+    for (uint32_t round = 0;; ++round) {
+        const int p = *reinterpret_cast<volatile int32_t*>(&bars->sched_pair[round & 1]);
+        if (p >= n_pairs) break;
+        const int it = 2 * p + (int)rank, it_peer = 2 * p + (int)(rank ^ 1);
+        const bool has = it < n_items;
+        int4 w0 = make_int4(0, 0, 0, 0), w1 = make_int4(0, 0, 0, 0);
+        if (has) {
+            w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
+            w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
+        }
+        bool shared = false;
+        if (has && it_peer < n_items) {
+            const int2 pw = *reinterpret_cast<const int2*>(items + (size_t)it_peer * LMI_ITEM_WORDS);
+            shared = pw.x == w0.x && pw.y == w0.y;  // same rows: two query tiles of one (bucket, range)
+        }
+        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
+        const int ntiles = has ? (nrows + SCAN_N - 1) / SCAN_N : 0;
+
+        if (warp == TMA_WARP) {
+            // ===================== TMA producer =====================
+            const uint64_t policy = ptx::policy_evict_normal();
+            uint32_t stage = 0;
+            for (int t = 0; t < ntiles; ++t) {
+                for (int s = 0; s < SPT; ++s) {
+                    const int kb0 = s * SCAN_BOXES;
+                    const int nb = min(SCAN_BOXES, KB - kb0);
+                    ptx::mbar_wait(&bars->empty[stage], ((use_bits >> stage) & 1u) ^ 1u);
+                    if (ptx::elect_one()) {
+                        uint8_t* dst = stages + (size_t)stage * SCAN_STAGE_BYTES;
+                        ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
+                        if (shared) {
+                            // this CTA's half of the stage (boxes b with b % 2 == rank), delivered to both CTAs
+                            for (int b = (int)rank; b < nb; b += 2)
+                                ptx::tma_load_2d_mcast(dst + b * SCAN_BOX_BYTES, &tmap, (kb0 + b) * SCAN_KBLK,
+                                                       row0 + t * SCAN_N, &bars->full[stage], (uint16_t)3, policy);
+                        } else {
+                            for (int b = 0; b < nb; ++b)
+                                ptx::tma_load_2d(dst + b * SCAN_BOX_BYTES, &tmap, (kb0 + b) * SCAN_KBLK, row0 + t * SCAN_N,
+                                                 &bars->full[stage], policy);
+                        }
+                    }
+                    __syncwarp();
+                    use_bits ^= 1u << stage;
+                    if (++stage == SCAN_STAGES) stage = 0;
+                }
+            }
+        } else if (warp >= MMA_WARP) {
+            // ===================== MMA issuers (alternate by score tile, as in scan_topk_tc_kernel) ========
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
+            const uint64_t desc0 = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(stages));
+            const uint32_t desc0_lo = (uint32_t)desc0;
+            const uint64_t desc0_hi = desc0 >> 32;
+            if (has) {
+                ptx::mbar_wait(&bars->q_ready, item_parity);
+                item_parity ^= 1;
+                ptx::tc_fence_after();
+            }
+            uint32_t stage = 0;
+            for (int t = 0; t < ntiles; ++t, ++tcount) {
+                const uint32_t buf = tcount & 1;
+                if (buf != mw) {  // the other issuer's tile: account for its stages
+                    for (int s = 0; s < SPT; ++s) {
+                        use_bits ^= 1u << stage;
+                        if (++stage == SCAN_STAGES) stage = 0;
+                    }
+                    continue;
+                }
+                ptx::mbar_wait(&bars->acc_empty[buf], ((tcount >> 1) & 1) ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem + TMEM_ACC_COL + buf * SCAN_N;
+                for (int s = 0; s < SPT; ++s) {
+                    const int kb0 = s * SCAN_BOXES;
+                    const int nb = min(SCAN_BOXES, KB - kb0);
+                    ptx::mbar_wait(&bars->full[stage], (use_bits >> stage) & 1u);
+                    ptx::tc_fence_after();
+                    if (ptx::elect_one()) {
+                        const uint32_t dlo = desc0_lo + ((stage * SCAN_STAGE_BYTES) >> 4);
+                        const uint32_t a0 = tmem + kb0 * (SCAN_KBLK / 2);
+                        if (nb == SCAN_BOXES) {
+#pragma unroll
+                            for (int b = 0; b < SCAN_BOXES; ++b) {
+#pragma unroll
+                                for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                                    const uint64_t b_desc =
+                                        (desc0_hi << 32) | (uint64_t)(dlo + ((b * SCAN_BOX_BYTES + k * 32) >> 4));
+                                    ptx::mma_f16_ts(d_tmem, a0 + b * (SCAN_KBLK / 2) + k * 8, b_desc, idesc,
+                                                    (b | k) != 0 ? 1u : (s != 0 ? 1u : 0u));
+                                }
+                            }
+                        } else {
+                            for (int b = 0; b < nb; ++b) {
+#pragma unroll
+                                for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                                    const uint64_t b_desc =
+                                        (desc0_hi << 32) | (uint64_t)(dlo + ((b * SCAN_BOX_BYTES + k * 32) >> 4));
+                                    ptx::mma_f16_ts(d_tmem, a0 + b * (SCAN_KBLK / 2) + k * 8, b_desc, idesc,
+                                                    (s | b | k) != 0 ? 1u : 0u);
+                                }
+                            }
+                        }
+                        if (shared) {
+                            ptx::mma_commit_mcast(&bars->empty[stage], (uint16_t)3);  // frees the stage in BOTH CTAs
+                        } else {
+                            ptx::mma_commit(&bars->empty[stage]);
+                            ptx::mma_commit(&bars->empty[stage]);
+                        }
+                        if (s == SPT - 1) ptx::mma_commit(&bars->acc_full[buf]);
+                    }
+                    __syncwarp();
+                    use_bits ^= 1u << stage;
+                    if (++stage == SCAN_STAGES) stage = 0;
+                }
+            }
+        } else if (has) {
+            // ===================== epilogue warps (thread == query row), as in scan_topk_tc_kernel ==========
+            const int q4 = warp & 3, h = warp >> 2;
+            const int row = q4 * 32 + lane;
+            const uint32_t lane_field = static_cast<uint32_t>(q4 * 32) << 16;
+            float* gate_mine = gates + h * SCAN_M + row;
+            const float* gate_other = gates + (h ^ 1) * SCAN_M + row;
+            const bool valid = row < mvalid;
+            const int q = valid ? (pair_list[slot0 + row] / B) : 0;
+            const uint4* qsrc = reinterpret_cast<const uint4*>(Q + (size_t)q * d);
+            auto load_kblock = [&](uint32_t (&r)[32], int c) {
+                if (valid) {
+#pragma unroll
+                    for (int v = 0; v < 8; ++v) {
+                        const uint4 u = __ldg(qsrc + c * 8 + v);
+                        r[4 * v + 0] = u.x;
+                        r[4 * v + 1] = u.y;
+                        r[4 * v + 2] = u.z;
+                        r[4 * v + 3] = u.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int v = 0; v < 32; ++v) r[v] = 0u;
+                }
+            };
+            {
+                uint32_t ra[32], rb[32];
+                int c = h;
+                if (c < KB) load_kblock(ra, c);
+                while (c < KB) {
+                    if (c + 2 < KB) load_kblock(rb, c + 2);
+                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), ra);
+                    c += 2;
+                    if (c >= KB) break;
+                    if (c + 2 < KB) load_kblock(ra, c + 2);
+                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), rb);
+                    c += 2;
+                }
+            }
+            ptx::tmem_st_wait();
+            *gate_mine = -INFINITY;
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(&bars->q_ready);
+
+            TopK tk;
+            tk.reset();
+            float tau = -INFINITY;
+            for (int t = 0; t < ntiles; ++t, ++tcount) {
+                const uint32_t buf = tcount & 1;
+                ptx::mbar_wait(&bars->acc_full[buf], (tcount >> 1) & 1);
+                ptx::tc_fence_after();
+                uint32_t v[32];
+                ptx::tmem_ld32(tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N + h * 32, v);
+                const float og = *gate_other;
+                tau = fmaxf(tau, og - fabsf(og) * 2.4e-7f);
+                ptx::tmem_ld_wait();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&bars->acc_empty[buf]);
+
+                const int base_row = row0 + t * SCAN_N + h * 32;
+                const int lim = nrows - t * SCAN_N - h * 32;
+                if (lim < 32) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j >= lim) v[j] = 0xff800000u;  // -inf
+                }
+                float g[4];
+#pragma unroll
+                for (int gi = 0; gi < 4; ++gi) {
+                    float m = __uint_as_float(v[gi * 8]);
+#pragma unroll
+                    for (int j = 1; j < 8; ++j) m = fmaxf(m, __uint_as_float(v[gi * 8 + j]));
+                    g[gi] = m;
+                }
+                const float mall = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
+                if (__any_sync(0xffffffffu, mall > tau)) {
+#pragma unroll
+                    for (int gi = 0; gi < 4; ++gi) {
+                        if (__any_sync(0xffffffffu, g[gi] > tau)) {
+                            uint32_t mask = 0;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                mask |= (__uint_as_float(v[gi * 8 + j]) > tau) ? (1u << j) : 0u;
+                            while (__any_sync(0xffffffffu, mask != 0)) {
+                                if (mask != 0) {
+                                    const int j = __ffs(mask) - 1;
+                                    mask &= mask - 1;
+                                    const uint32_t a0 = (j & 1) ? v[gi * 8 + 1] : v[gi * 8 + 0];
+                                    const uint32_t a1 = (j & 1) ? v[gi * 8 + 3] : v[gi * 8 + 2];
+                                    const uint32_t a2 = (j & 1) ? v[gi * 8 + 5] : v[gi * 8 + 4];
+                                    const uint32_t a3 = (j & 1) ? v[gi * 8 + 7] : v[gi * 8 + 6];
+                                    const uint32_t b0 = (j & 2) ? a1 : a0;
+                                    const uint32_t b1 = (j & 2) ? a3 : a2;
+                                    const float f = __uint_as_float((j & 4) ? b1 : b0);
+                                    if (f > tau) {
+                                        tk.insert(f, base_row + gi * 8 + j);
+                                        tau = fmaxf(tau, tk.s[TOPK - 1]);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    *gate_mine = tk.s[TOPK - 1];
+                }
+            }
+            if (valid)
+                store_topk(tk, part_sim, part_row, ((size_t)(slot0 + row) * lmax + list0 + h) * TOPK);
+        }
+
+        // ---- end of the pair: publish the next pair index, then the cluster barrier ----
+        if (scheduler) {
+            publish_pair((round + 1) & 1, next_p);
+            next_p = atomicAdd(sched_counter, 1);
+        }
+        __syncwarp();
+        ptx::cluster_arrive();
+        ptx::cluster_wait();
+    }
+
+    ptx::tc_fence_before();
+    ptx::cluster_sync();
+    if (warp == MMA_WARP) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem, TMEM_COLS);
+    }
+}
+
 // Verification kernel (tests only): same item list, same top-k bookkeeping, plain fp32
 // FMA dot products on CUDA cores.  One block per item, thread == query row.
 __global__ void __launch_bounds__(SCAN_M)
@@ -578,7 +910,7 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
             lmax, part_sim, part_row);
         return static_cast<int>(cudaGetLastError());
     }
-    if (impl != 0) return LMI_E_BADARG;
+    if (impl != 0 && impl != 2) return LMI_E_BADARG;
     if (d % lmi::SCAN_KBLK != 0 || d > lmi::SCAN_MAX_D) return LMI_E_UNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(X) & 15) != 0 || (reinterpret_cast<uintptr_t>(Q) & 15) != 0) return LMI_E_BADARG;
 
@@ -601,6 +933,24 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
                                              (int)lmi::SCAN_SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    if (impl == 2) {
+        // cluster-of-2 kernel: TMA multicast between the query tiles of one (bucket, row range)
+        static bool pair_attr_set[64] = {};
+        if (dev < 0 || dev >= 64 || !pair_attr_set[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(lmi::scan_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)lmi::SCAN_SMEM_BYTES);
+            if (e != cudaSuccess) return (int)e;
+            if (dev >= 0 && dev < 64) pair_attr_set[dev] = true;
+        }
+        int64_t clusters = (max_items + 1) / 2;
+        if (clusters > sms / 2) clusters = sms / 2;
+        if (clusters < 1) clusters = 1;
+        cudaError_t me = cudaMemsetAsync(const_cast<int32_t*>(n_items) + 1, 0, sizeof(int32_t), st);
+        if (me != cudaSuccess) return (int)me;
+        lmi::scan_topk_pair_kernel<<<(unsigned)(2 * clusters), lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
+            tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row);
+        return static_cast<int>(cudaGetLastError());
     }
     const int grid = (int)(max_items < (int64_t)sms ? max_items : (int64_t)sms);
     int dbg = 0;

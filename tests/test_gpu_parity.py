@@ -155,7 +155,7 @@ def test_invert_matches_numpy():
             assert len({it[1] for it in exp_items}) > 1
 
 
-@pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("impl", [1, 0, 2], ids=["simt", "tcgen05", "tcgen05_pair"])
 @pytest.mark.parametrize("name", case_names())
 def test_search_matches_reference_golden(name, impl):
     c = GoldenCase(name)
@@ -186,7 +186,7 @@ def _synthetic(n, nq, C, seed_centres=300, steps=80):
     return X.numpy(), Q.numpy(), syn.layers_to_numpy(layers), pred.numpy()
 
 
-@pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("impl", [1, 0, 2], ids=["simt", "tcgen05", "tcgen05_pair"])
 def test_search_matches_oracle_medium(impl):
     """Ragged real-sized buckets, several ranges per bucket, partial query tiles."""
     n, nq, C, B = 60_000, 1500, 24, 4
@@ -217,6 +217,40 @@ def test_many_ranges_per_bucket(monkeypatch):
     same = (li.last_bucket_order.cpu().numpy() == exp_order[:, :, 0]).all(axis=1)
     assert same.mean() > 0.99
     assert_search_parity(d[same], i[same], exp_d[same], exp_i[same], what="many ranges")
+
+
+@pytest.mark.parametrize("d", [768, 64, 96, 320])
+def test_cluster_pair_scan_equals_single_cta_scan(d, monkeypatch):
+    """lmi_scan_topk impl 2 (clusters of two CTAs, bucket rows shared by TMA multicast) against impl 0, bit for
+    bit: odd and even numbers of query tiles per bucket (shared and independent pairs, an idle partner at the
+    end of the list), several ranges per bucket, one-box and partial pipeline stages (d = 64: one k-block,
+    d = 96 -> 128: two, d = 320: five), budgets that touch every bucket."""
+    monkeypatch.setenv("LMI_RANGE_ROWS", "4096")
+    from learnedmetricindex_b200 import DeviceBucketLayout
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(d)
+    C, nq = 7, 1100
+    sizes = np.array([9000, 300, 12000, 5, 20000, 64, 4100])
+    n = int(sizes.sum())
+    pred = rs.permutation(np.repeat(np.arange(C), sizes)).astype(np.int64)
+    X = rs.standard_normal((n, d)).astype(np.float32)
+    X = (X / np.linalg.norm(X, axis=1, keepdims=True)).astype(np.float16)
+    Q = rs.standard_normal((nq, d)).astype(np.float32)
+    Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+    layers = seeded_layers(d + 1, "MLP", d, C, scale=2.0)
+    layout = DeviceBucketLayout.from_host(X, pred, C)
+    qd = torch.from_numpy(Q).cuda()
+    for B, k in [(1, 10), (2, 10), (3, 7), (C, 10)]:
+        out = {}
+        for impl in (0, 2):
+            li = _index(layers, C, scan_impl=impl)
+            li.attach_layout(layout)
+            for rep in range(2):
+                dd, ii = li.search_device(qd, qd, [C], B, k)
+            out[impl] = (dd.clone(), ii.clone(), int(li.last_plan["n_items"][0]))
+        assert out[0][2] == out[2][2] and out[0][2] > 8
+        assert torch.equal(out[0][0], out[2][0]) and torch.equal(out[0][1], out[2][1]), (d, B, k)
 
 
 def test_f32_queries_and_float_inputs():

@@ -1,0 +1,98 @@
+#!/usr/bin/env python
+"""A/B of the scan's scheduling knobs on the headline workload (tuning aid, not a benchmark).
+
+Builds the 10M x 768 index once, then for every configuration -- environment overrides of plan_scan
+(LMI_RANGE_ROWS / LMI_TAIL_ROWS / LMI_TAIL_PERMILLE) and lmi_scan_topk tuning flags (LMI_SCAN_FLAGS) --
+times `steps` back-to-back searches with an event around every scan launch, samples the clocks, and checks
+that the result is bit-identical to the first configuration's (the knobs must never change results).
+
+    python tools/scan_lab.py [--n 10000000] [--steps 40] [--configs "name:K=V,K=V;name2:..."]
+"""
+import argparse, json, os, sys, time, types
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+import bench
+
+DEFAULT = ("one_level:LMI_TAIL_PERMILLE=0;"
+           "two_level_default:;"
+           "tail_8192_100:LMI_TAIL_ROWS=8192,LMI_TAIL_PERMILLE=100;"
+           "tail_8192_250:LMI_TAIL_ROWS=8192,LMI_TAIL_PERMILLE=250;"
+           "l2_siblings:LMI_SCAN_FLAGS=1;"
+           "pair_one_level:LMI_SCAN_IMPL=2,LMI_TAIL_PERMILLE=0;"
+           "pair_two_level:LMI_SCAN_IMPL=2;"
+           "pair_tail_100:LMI_SCAN_IMPL=2,LMI_TAIL_ROWS=8192,LMI_TAIL_PERMILLE=100")
+ap = argparse.ArgumentParser()
+ap.add_argument("--n", type=int, default=10_000_000)
+ap.add_argument("--nq", type=int, default=10_000)
+ap.add_argument("--probe", type=int, default=4)
+ap.add_argument("--steps", type=int, default=12, help="searches per burst")
+ap.add_argument("--rounds", type=int, default=8, help="round-robin passes over the configurations")
+ap.add_argument("--configs", default=DEFAULT)
+ap.add_argument("--out", default="")
+a = ap.parse_args()
+args = types.SimpleNamespace(n=a.n, nq=a.nq, buckets=120, centres=2000, noise=0.25, latent=24, train_steps=300)
+dev = torch.device("cuda", 0)
+torch.cuda.set_device(0)
+from learnedmetricindex_b200 import DeviceBucketLayout, LearnedIndex
+w = bench.build_workload(args, dev, 0, 1)
+layout = DeviceBucketLayout(w["vectors"], torch.from_numpy(w["bucket_off"]), w["ids"])
+Q = w["Q"]
+KNOBS = ("LMI_RANGE_ROWS", "LMI_TAIL_ROWS", "LMI_TAIL_PERMILLE", "LMI_SCAN_FLAGS", "LMI_SCAN_IMPL")
+# every configuration gets its own index object (the knobs are read when it plans its first search); the timed
+# bursts are INTERLEAVED round-robin, so the board's power/thermal state is the same for all of them
+cfgs = []
+ref = None
+for spec in [c for c in a.configs.split(";") if c]:
+    name, _, kv = spec.partition(":")
+    for kname in KNOBS:
+        os.environ.pop(kname, None)
+    for item in [x for x in kv.split(",") if x]:
+        kk, vv = item.split("=")
+        os.environ[kk] = vv
+    li = LearnedIndex(w["layers"], {}, [(i,) for i in range(120)])  # reads the knobs
+    li.attach_layout(layout)
+    for _ in range(3):
+        d, i = li.search_device(Q, Q, [120], a.probe, 10)
+    torch.cuda.synchronize()
+    if ref is None:
+        ref = (d.clone(), i.clone())
+    same = bool(torch.equal(d, ref[0]) and torch.equal(i, ref[1]))
+    cfgs.append(dict(name=name, env=kv, li=li, same=same, scan=[], step=[], mhz=[],
+                     plan={k: v for k, v in li.last_plan.items() if isinstance(v, int)},
+                     n_items=int(li.last_plan["n_items"][0])))
+    print(f"# {name}: result_equal_to_first_config={same} plan={cfgs[-1]['plan']} n_items={cfgs[-1]['n_items']}", flush=True)
+for kname in KNOBS:
+    os.environ.pop(kname, None)
+for rnd in range(a.rounds):
+    order = cfgs if rnd % 2 == 0 else cfgs[::-1]
+    for c in order:
+        li = c["li"]
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(a.steps)]
+        smp = bench.ClockSampler(0, period_s=0.005)
+        smp.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_a = time.time()
+        e0.record()
+        for e in evs:
+            li.search_device(Q, Q, [120], a.probe, 10, events=e)
+        e1.record()
+        torch.cuda.synchronize()
+        t_b = time.time()
+        smp.stop()
+        c["scan"] += [e[2].elapsed_time(e[3]) for e in evs]
+        c["step"].append(e0.elapsed_time(e1) / a.steps)
+        c["mhz"].append(smp.summary([(t_a, t_b)]).get("sm_mhz"))
+rows = []
+for c in cfgs:
+    row = dict(config=c["name"], env=c["env"], plan=c["plan"], n_items=c["n_items"],
+               scan_ms_mean=float(np.mean(c["scan"])), scan_ms_median=float(np.median(c["scan"])),
+               scan_ms_min=float(np.min(c["scan"])), step_ms=float(np.mean(c["step"])),
+               sm_mhz_per_round=c["mhz"], result_equal_to_first_config=c["same"])
+    rows.append(row)
+    print(json.dumps(row), flush=True)
+if a.out:
+    with open(a.out, "w") as f:
+        for r in rows:
+            f.write(json.dumps(r) + "\n")
