@@ -7,6 +7,7 @@
  * Each entry point below replaces one of them (file:line relative to the
  * reference checkout):
  *
+ *   lmi_mlp_topn (ONE launch) or
  *   lmi_linear_tc (+ lmi_split_tf32) / lmi_linear / lmi_softmax_topn
  *                                  <- NeuralNetwork.predict_proba
  *                                     search/li/model.py:226-241 (Linear/ReLU
@@ -52,7 +53,7 @@
 extern "C" {
 #endif
 
-#define LMI_B200_ABI_VERSION 4
+#define LMI_B200_ABI_VERSION 5
 
 #define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
 #define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
@@ -102,6 +103,24 @@ int lmi_linear_tc_grouped(const float *x_hi, const float *x_mid, const float *x_
  * bucket_order int32[nq,B] (== the reference's bucket_order[:, :, 0]), probs f32[nq,B]. */
 int lmi_softmax_topn(const float *logits, int nq, int C, int B,
                      int32_t *bucket_order, float *probs, void *stream);
+
+/* NeuralNetwork.predict_proba (model.py:226-241) of a 2-Linear-layer model (MLP, MLP-2, MLP-3, MLP-4,
+ * model.py:29-79) in ONE launch, with the slice bucket_order = classes[:, :B] (LearnedIndex.py:209-214):
+ * Linear + bias + ReLU + Linear + bias + softmax + top-B, the hidden activations never leaving the SM.
+ * Same split-tf32 arithmetic as lmi_linear_tc (fp32-quality logits); x is the fp16 query matrix (exact
+ * in one tf32 part), w1/w2 parts from lmi_split_tf32 of the [hidden,in_dim] / [C,hidden] weights.
+ *   lmi_mlp_topn_supported  1 when the shape is implemented: fp16 x, in_dim % 8 == 0, hidden % 64 == 0,
+ *                           hidden <= 1024, C <= 128, B <= C; otherwise use the four-call path above
+ *   workspace   lmi_mlp_topn_workspace_bytes(nq, hidden, C) bytes, 16-byte aligned, ZEROED ONCE by the
+ *               caller before the first use (the kernel leaves its tile counters at zero again)
+ *   B > 0:  bucket_order int32[nq,B], probs f32[nq,B] as lmi_softmax_topn;  logits f32[nq,C] optional
+ *   B == 0: only logits are written (predict / multi-level tables) */
+int lmi_mlp_topn_supported(int x_is_f16, int in_dim, int hidden, int C, int B);
+int64_t lmi_mlp_topn_workspace_bytes(int nq, int hidden, int C);
+int lmi_mlp_topn(const void *x_f16, int nq, int in_dim,
+                 const float *w1_hi, const float *w1_mid, const float *w1_lo, const float *b1, int hidden,
+                 const float *w2_hi, const float *w2_mid, const float *w2_lo, const float *b2, int C, int B,
+                 void *workspace, int32_t *bucket_order, float *probs, float *logits, void *stream);
 
 /* argmax over the C logits of each row (first maximum), int64 out. */
 int lmi_argmax(const float *logits, int64_t n, int C, int64_t *out, void *stream);

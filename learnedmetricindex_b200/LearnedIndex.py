@@ -346,7 +346,7 @@ class LearnedIndex:
     @property
     def launches_per_search(self) -> int:
         """Kernels of this library one 1-level search launches (navigation + inversion + scan + merge)."""
-        return self.root_model.launches_per_topn + 3 + 1 + 1
+        return self.root_model.launches_per_topn() + 3 + 1 + 1
 
     def _surface_query_rounding(self):
         """After a host-visible sync: did the fp16 copy of the last f32 query batch change any value?"""
@@ -406,8 +406,11 @@ class LearnedIndex:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
                 d, i = self.search_device(sn, ss, n_categories, n_buckets, k, events=ev, out=(d, i))
+            # the graph holds raw pointers into the batch workspace and the navigation workspace: keep both alive
+            # with the entry, whatever the workspace caches evict
             entry = dict(graph=graph, qn=sn, qs=ss, dists=d, nns=i, events=ev, order=self.last_bucket_order,
-                         plan=self.last_plan)
+                         plan=self.last_plan, keep=(getattr(self, "_last_ws", None),
+                                                    dict(self.root_model._fused_ws)))
             self._graphs[key] = entry
         else:
             self._graphs.move_to_end(key)

@@ -14,7 +14,7 @@ from ctypes import c_char_p, c_int, c_int64, c_void_p
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "liblmi_b200.so")
-SOURCES = ["lmi_mlp.cu", "lmi_mlp_tc.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu", "lmi_navigate.cu"]
+SOURCES = ["lmi_mlp.cu", "lmi_mlp_tc.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu", "lmi_navigate.cu", "lmi_nav_fused.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
@@ -65,6 +65,11 @@ _SIGNATURES = {
                                       c_int, c_int, c_void_p]),
     "lmi_softmax_segments": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
     "lmi_softmax_topn": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "lmi_mlp_topn_supported": (c_int, [c_int, c_int, c_int, c_int, c_int]),
+    "lmi_mlp_topn_workspace_bytes": (c_int64, [c_int, c_int, c_int]),
+    "lmi_mlp_topn": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                             c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                             c_void_p]),
     "lmi_argmax": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "lmi_softmax_probs": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p]),
     "lmi_navigate_tree": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p,

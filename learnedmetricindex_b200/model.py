@@ -23,6 +23,11 @@ HIDDEN_LAYERS = {
 }
 
 
+# lmi_mlp_topn keeps per-(query tile, hidden chunk) partial logits in its workspace (4 KB per query for MLP-4 with
+# 120 buckets): fine for a query batch, too much for the million-row chunks of the layout build's predict()
+FUSED_LOGITS_MAX_ROWS = 32768
+
+
 def _stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -71,14 +76,18 @@ class NeuralNetwork:
             assert W1.shape[1] == W0.shape[0], "layer shapes do not chain"
         self.input_dim = self.layers[0][0].shape[1]
         self.n_output_neurons = self.layers[-1][0].shape[0]
-        # "tc": tcgen05 tf32 split-precision GEMM (product path); "ffma": fp32 CUDA-core kernel
-        # (verification, and the fallback for input widths that are not a multiple of 4)
-        self.impl = os.environ.get("LMI_MLP_IMPL", "tc")
+        # "fused": the whole predict_proba in ONE launch (lmi_mlp_topn) where the shape allows, else "tc";
+        # "tc": tcgen05 tf32 split-precision GEMM per layer + softmax/top-n launch (the check of "fused", and the
+        # path of every other shape); "ffma": fp32 CUDA-core kernel (verification, and the fallback for input
+        # widths that are not a multiple of 4)
+        self.impl = os.environ.get("LMI_MLP_IMPL", "fused")
         self._w_parts: Optional[List[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]] = None
+        self._fused_ws: dict = {}  # nq -> zero-initialised workspace of lmi_mlp_topn
 
-    @property
-    def launches_per_topn(self) -> int:
-        """Kernel launches of one ``topn_device`` call (input split + one per layer + softmax/top-n)."""
+    def launches_per_topn(self, x_is_f16: bool = True, n_top: int = 1) -> int:
+        """Kernel launches of one ``topn_device`` call: 1 fused, else input split + one per layer + softmax/top-n."""
+        if self._fused_ok(x_is_f16, n_top):
+            return 1
         return (1 if self._tc_ok() else 0) + len(self.layers) + 1
 
     # -- construction from the reference's objects ------------------------------------
@@ -120,7 +129,45 @@ class NeuralNetwork:
         return hi, mid, lo
 
     def _tc_ok(self) -> bool:
-        return self.impl == "tc" and all(W.shape[1] % 4 == 0 for W, _ in self.layers)
+        return self.impl in ("tc", "fused") and all(W.shape[1] % 4 == 0 for W, _ in self.layers)
+
+    def _fused_ok(self, x_is_f16: bool, n_top: int) -> bool:
+        if self.impl != "fused" or len(self.layers) != 2:
+            return False
+        (W1, _), (W2, _) = self.layers
+        return bool(_native.lib().lmi_mlp_topn_supported(int(x_is_f16), W1.shape[1], W1.shape[0], W2.shape[0],
+                                                         int(n_top)))
+
+    def _weight_parts(self):
+        if self._w_parts is None:
+            self._w_parts = [self._split(W, False) for W, _ in self.layers]
+        return self._w_parts
+
+    def _fused(self, x: torch.Tensor, n_top: int, want_logits: bool = False):
+        """One launch of ``lmi_mlp_topn``: (order, probs, logits-or-None)."""
+        L = _native.lib()
+        nq = x.shape[0]
+        (W1, b1), (W2, b2) = self.layers
+        H, C = W1.shape[0], W2.shape[0]
+        ws = self._fused_ws.get(nq)
+        if ws is None:
+            if len(self._fused_ws) >= 16:
+                self._fused_ws.pop(next(iter(self._fused_ws)))
+            ws = torch.zeros(int(L.lmi_mlp_topn_workspace_bytes(nq, H, C)), dtype=torch.uint8, device=self.device)
+            self._fused_ws[nq] = ws
+        (h1, m1, l1), (h2, m2, l2) = self._weight_parts()
+        order = probs = logits = None
+        if n_top > 0:
+            order = torch.empty((nq, n_top), dtype=torch.int32, device=self.device)
+            probs = torch.empty((nq, n_top), dtype=torch.float32, device=self.device)
+        if want_logits or n_top == 0:
+            logits = torch.empty((nq, C), dtype=torch.float32, device=self.device)
+        ptr = lambda t: t.data_ptr() if t is not None else None
+        _native.check(L.lmi_mlp_topn(x.data_ptr(), nq, W1.shape[1], h1.data_ptr(), m1.data_ptr(), l1.data_ptr(),
+                                     b1.data_ptr(), H, h2.data_ptr(), m2.data_ptr(), l2.data_ptr(), b2.data_ptr(), C,
+                                     int(n_top), ws.data_ptr(), ptr(order), ptr(probs), ptr(logits), _stream_ptr()),
+                      "lmi_mlp_topn")
+        return order, probs, logits
 
     def split_input(self, x: torch.Tensor):
         """The tf32 parts of a query matrix for ``logits(x, parts=...)`` -- shared by every model of
@@ -135,9 +182,10 @@ class NeuralNetwork:
         assert x.is_cuda and x.dim() == 2 and x.is_contiguous()
         assert x.shape[1] == self.input_dim, (x.shape, self.input_dim)
         nq = x.shape[0]
+        if 0 < nq <= FUSED_LOGITS_MAX_ROWS and parts is None and self._fused_ok(x.dtype == torch.float16, 0):
+            return self._fused(x, 0)[2]
         if nq > 0 and self._tc_ok():
-            if self._w_parts is None:
-                self._w_parts = [self._split(W, False) for W, _ in self.layers]
+            self._weight_parts()
             ptr = lambda t: t.data_ptr() if t is not None else None
             if parts is None:
                 parts = self.split_input(x)
@@ -168,6 +216,10 @@ class NeuralNetwork:
     def topn_device(self, x: torch.Tensor, n_top: int) -> Tuple[torch.Tensor, torch.Tensor]:
         """(bucket ids int32[nq,n_top], probabilities f32[nq,n_top]) on the device."""
         L = _native.lib()
+        assert x.is_cuda and x.dim() == 2 and x.is_contiguous() and x.shape[1] == self.input_dim
+        if x.shape[0] > 0 and n_top > 0 and self._fused_ok(x.dtype == torch.float16, n_top):
+            order, probs, _ = self._fused(x, n_top)
+            return order, probs
         logits = self.logits(x)
         nq, C = logits.shape
         order = torch.empty((nq, n_top), dtype=torch.int32, device=self.device)

@@ -37,13 +37,20 @@ def _order_rows_equal(got, exp, probs, tol=1e-6):
 
 
 @pytest.mark.parametrize("name", case_names())
-@pytest.mark.parametrize("mlp_impl", ["tc", "ffma"])
+@pytest.mark.parametrize("mlp_impl", ["fused", "tc", "ffma"])
 def test_mlp_matches_reference_golden(name, mlp_impl):
     c = GoldenCase(name)
     C = c.n_categories[0]
     li = _index(c.layers, C)
-    li.root_model.impl = mlp_impl  # "tc": tcgen05 tf32 split GEMM (product path); "ffma": fp32 CUDA-core kernel
-    probs, classes = li.root_model.predict_proba(c.Q)
+    # "fused": one-launch lmi_mlp_topn (product path where the shape allows; fp16 queries); "tc": tcgen05 tf32 split
+    # GEMM per layer + softmax/top-n; "ffma": fp32 CUDA-core kernel
+    li.root_model.impl = mlp_impl
+    Q = c.Q
+    if mlp_impl == "fused":
+        Q16 = np.asarray(Q).astype(np.float16)
+        if (Q16.astype(np.float32) == np.asarray(Q, dtype=np.float32)).all():
+            Q = Q16  # same values, and the dtype the one-launch kernel takes
+    probs, classes = li.root_model.predict_proba(Q)
     assert probs.dtype == np.float32 and classes.dtype == np.int64 and classes.shape == c.classes.shape
     np.testing.assert_allclose(probs, c.probs, rtol=2e-5, atol=1e-7)
     _order_rows_equal(classes, c.classes, c.probs)
@@ -71,13 +78,49 @@ def test_mlp_tensor_core_logits_have_fp32_quality():
                 if li_ == 0:
                     h = np.maximum(h, 0)
             errs = {}
-            for impl in ("tc", "ffma"):
+            for impl in ("fused", "tc", "ffma"):
                 net = NeuralNetwork(layers)
                 net.impl = impl
                 out = net.logits(torch.from_numpy(xq).cuda()).cpu().numpy().astype(np.float64)
                 errs[impl] = np.abs(out - h).max()
             scale = np.abs(h).max()
             assert errs["tc"] <= max(2 * errs["ffma"], 4e-7 * scale), (nq, d, H, C, xq.dtype, errs, scale)
+            assert errs["fused"] <= max(2 * errs["ffma"], 4e-7 * scale), (nq, d, H, C, xq.dtype, errs, scale)
+
+
+def test_mlp_one_launch_equals_per_layer_path():
+    """lmi_mlp_topn (Linear+ReLU+Linear+softmax+top-B in one launch) against the per-layer path it replaces:
+    same probed-bucket lists (probability ties <= 1e-6 excepted), same probabilities, over every hidden width of
+    the reference's 2-layer zoo (model.py:29-79), ragged last query tiles, class counts that are not multiples of
+    16, B = 1 .. C, and repeated launches on one workspace (the tile counters must come back to zero)."""
+    from learnedmetricindex_b200 import NeuralNetwork, _native
+
+    L = _native.lib()
+    rs = np.random.RandomState(11)
+    shapes = [(10000, 768, 512, 120, 4), (1, 768, 512, 120, 120), (129, 96, 128, 100, 10), (300, 64, 64, 7, 7),
+              (1000, 768, 256, 128, 1), (513, 200, 1024, 33, 5), (77, 8, 64, 1, 1)]
+    for nq, d, H, C, B in shapes:
+        assert L.lmi_mlp_topn_supported(1, d, H, C, B) == 1
+        layers = [(rs.randn(H, d).astype(np.float32) / np.sqrt(d), rs.randn(H).astype(np.float32) * 0.1),
+                  (rs.randn(C, H).astype(np.float32) * (3.0 / np.sqrt(H)), rs.randn(C).astype(np.float32) * 0.1)]
+        x = torch.from_numpy(rs.randn(nq, d).astype(np.float16)).cuda()
+        ref = NeuralNetwork(layers)
+        ref.impl = "tc"
+        exp_o, exp_p = ref.topn_device(x, B)
+        exp_all = ref.topn_device(x, C)[1].cpu().numpy()
+        net = NeuralNetwork(layers)
+        assert net.impl == "fused" and net.launches_per_topn(True, B) == 1
+        for rep in range(3):
+            got_o, got_p = net.topn_device(x, B)
+            torch.cuda.synchronize()
+            np.testing.assert_allclose(got_p.cpu().numpy(), exp_p.cpu().numpy(), rtol=2e-5, atol=1e-7,
+                                       err_msg=f"{(nq, d, H, C, B)} rep {rep}")
+            _order_rows_equal(got_o.cpu().numpy(), exp_o.cpu().numpy(), exp_all)
+        np.testing.assert_allclose(net.logits(x).cpu().numpy(), ref.logits(x).cpu().numpy(), rtol=2e-6, atol=4e-6)
+    # shapes the one-launch kernel does not take fall through to the per-layer path
+    assert L.lmi_mlp_topn_supported(0, 768, 512, 120, 4) == 0  # f32 queries
+    assert L.lmi_mlp_topn_supported(1, 768, 16, 8, 4) == 0     # hidden width below one chunk
+    assert L.lmi_mlp_topn_supported(1, 768, 512, 200, 4) == 0  # more than 128 classes
 
 
 def test_invert_matches_numpy():
