@@ -848,6 +848,10 @@ def measure(args, wl_name, device, rank, world, local_rank, headline):
                 d_1, i_1 = li1.search_device(Q, Q, [C], B, K_NN)
                 torch.cuda.synchronize()
                 same_unsharded = bool(torch.equal(d_1, d_p) and torch.equal(i_1, i_p))
+                if not same_unsharded:  # say what differs before failing
+                    nd, ni = int((d_1 != d_p).sum().item()), int((i_1 != i_p).sum().item())
+                    tied = int(((i_1 != i_p) & (d_1 == d_p)).sum().item())
+                    log(f"sharded vs unsharded: {nd} distances and {ni} ids differ ({tied} of the ids at equal distance)")
                 del w1, li1, d_1, i_1
                 torch.cuda.empty_cache()
             flag = torch.tensor([1 if same_unsharded else 0], dtype=torch.int32, device=device)

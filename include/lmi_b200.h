@@ -260,30 +260,39 @@ int lmi_scan_topk(const void *X, int64_t n, int d, const void *Q, int nq, int B,
  * earlier probe first (stable argsort over [previous | new], LearnedIndex.py:131-134).
  *   ids        uint32[n]   label of each bucket-major row (the DataFrame index)
  *   dists      f64[nq,k_out] out, nns uint32[nq,k_out] out
+ *   probe_rank uint16[nq,k_out] out, optional (NULL: not written): the probe rank r of each returned entry
+ *              (0xffff for a pad) -- what the cross-GPU merge needs to order equal distances exactly as
+ *              the single-GPU search does
  *   k_out <= 10*B.
  */
 int lmi_merge_topk(const float *part_sim, const int32_t *part_row, const int32_t *slot_of_pair,
                    const int32_t *bucket_order, const int64_t *bucket_off, const uint32_t *ids,
                    const int32_t *bucket_lists, int nq, int B, int C, int lmax, int k_out,
-                   double *dists, uint32_t *nns, void *stream);
+                   double *dists, uint32_t *nns, uint16_t *probe_rank, void *stream);
 
 /* Cross-GPU merge after the all-gather of the per-rank results: rank w's ascending
- * lists are dists_all + w*rank_stride_d (f64[nq,k]) and nns_all + w*rank_stride_i
- * (uint32[nq,k]) -- strides in elements, so one packed gather buffer works -- and the
- * output is the k smallest per query (ties keep the lower rank first). world <= 32. */
-int lmi_merge_ranks(const double *dists_all, const uint32_t *nns_all, int64_t rank_stride_d,
-                    int64_t rank_stride_i, int world, int nq, int k,
-                    double *dists, uint32_t *nns, void *stream);
+ * lists are dists_all + w*rank_stride_d (f64[nq,k]), nns_all + w*rank_stride_i
+ * (uint32[nq,k]) and probe_all + w*rank_stride_p (uint16[nq,k], lmi_merge_topk's probe_rank;
+ * NULL: absent) -- strides in elements, so one packed gather buffer works -- and the
+ * output is the k smallest per query.  Equal distances are ordered by (probe rank, GPU rank):
+ * with whole buckets per GPU, or with every bucket cut into row slices in GPU order, that is
+ * the single-GPU search's stable order (LearnedIndex.py:131-134), so the sharded result equals
+ * the unsharded one bit for bit.  Without probe ranks ties keep the lower GPU rank. world <= 32. */
+int lmi_merge_ranks(const double *dists_all, const uint32_t *nns_all, const uint16_t *probe_all,
+                    int64_t rank_stride_d, int64_t rank_stride_i, int64_t rank_stride_p,
+                    int world, int nq, int k, double *dists, uint32_t *nns, void *stream);
 
 /* The exchange step fused with the merge: instead of an all-gather followed by lmi_merge_ranks,
  * every rank reads its peers' result blocks straight out of peer memory (NVLink P2P through
  * NVSwitch) inside the merge kernel.  rank_base: DEVICE array of `world` pointers, entry w = the
- * address IN THIS PROCESS of rank w's packed block [dists f64[nq,k] | pad | nns u32[nq,k]]
- * (symmetric memory / CUDA IPC mapping); nns_offset_bytes = offset of the nns part in a block.
+ * address IN THIS PROCESS of rank w's packed block [dists f64[nq,k] | nns u32[nq,k] | probe u16[nq,k]]
+ * (symmetric memory / CUDA IPC mapping); nns_offset_bytes / probe_offset_bytes = offsets of those
+ * parts in a block (probe_offset_bytes < 0: no probe ranks, ties keep the lower GPU rank).
  * The caller orders the launch after a cross-rank barrier (all blocks written) and must not
  * overwrite its own block until every peer has passed the next barrier (double buffering). */
-int lmi_merge_ranks_peer(const void *const *rank_base, int64_t nns_offset_bytes, int world, int nq,
-                         int k, double *dists, uint32_t *nns, void *stream);
+int lmi_merge_ranks_peer(const void *const *rank_base, int64_t nns_offset_bytes,
+                         int64_t probe_offset_bytes, int world, int nq, int k, double *dists,
+                         uint32_t *nns, void *stream);
 
 /* All-gather by loads from peer memory (no collective library): dst[w*bytes_per_rank + i] =
  * rank_base[w][i] for every rank w; rank_base as in lmi_merge_ranks_peer, bytes_per_rank a multiple

@@ -297,8 +297,14 @@ class LearnedIndex:
         self.last_bucket_order, self.last_probs = order, probs
         mark(1)
 
+        probe_out = None
         if out is not None:
-            dists, nns = out
+            # (dists, nns) or (dists, nns, probe ranks int16[nq,k]) -- the third is what a cross-GPU merge needs to
+            # order equal distances like the unsharded search (lmi_merge_topk's probe_rank)
+            dists, nns = out[0], out[1]
+            if len(out) > 2:
+                probe_out = out[2]
+                assert probe_out.shape == (nq, k_out) and probe_out.element_size() == 2 and probe_out.is_contiguous()
             assert dists.shape == (nq, k_out) and dists.dtype == torch.float64 and dists.is_contiguous()
             assert nns.shape == (nq, k_out) and nns.dtype == torch.int32 and nns.is_contiguous()
         else:
@@ -338,7 +344,8 @@ class LearnedIndex:
         mark(3)
         _native.check(L.lmi_merge_topk(P[WS_PART_SIM], P[WS_PART_ROW], P[WS_SLOT_OF_PAIR], order.data_ptr(),
                                        layout.bucket_off.data_ptr(), layout.ids.data_ptr(), P[WS_BUCKET_LISTS], nq, B,
-                                       C, ws.lmax, k_out, dists.data_ptr(), nns.data_ptr(), st), "lmi_merge_topk")
+                                       C, ws.lmax, k_out, dists.data_ptr(), nns.data_ptr(),
+                                       probe_out.data_ptr() if probe_out is not None else None, st), "lmi_merge_topk")
         mark(4)
         self.last_plan = dict(plan, max_items=ws.max_items, n_items=ws.n_items, counts=ws.counts)
         return dists, nns

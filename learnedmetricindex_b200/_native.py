@@ -85,11 +85,12 @@ _SIGNATURES = {
     "lmi_scan_topk": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
                               c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "lmi_merge_topk": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
-                               c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
-    "lmi_merge_ranks": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
-                                c_void_p]),
+                               c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "lmi_merge_ranks": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int,
+                                c_void_p, c_void_p, c_void_p]),
     "lmi_gather_peer": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
-    "lmi_merge_ranks_peer": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "lmi_merge_ranks_peer": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
+                                     c_void_p]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -39,7 +39,8 @@ __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int3
                                   const int32_t* __restrict__ slot_of_pair, const int32_t* __restrict__ order,
                                   const int64_t* __restrict__ bucket_off, const uint32_t* __restrict__ ids,
                                   const int32_t* __restrict__ bucket_lists, int nq, int B, int C, int lmax,
-                                  int k_out, double* __restrict__ dists, uint32_t* __restrict__ nns) {
+                                  int k_out, double* __restrict__ dists, uint32_t* __restrict__ nns,
+                                  uint16_t* __restrict__ probe_out) {
     extern __shared__ float sm[];
     const int warps = blockDim.x >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -202,9 +203,11 @@ __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int3
             if (ke == 0x7fffffff) {
                 dists[(size_t)q * k_out + t] = INFINITY;
                 nns[(size_t)q * k_out + t] = 0u;
+                if (probe_out) probe_out[(size_t)q * k_out + t] = 0xffffu;
             } else {
                 dists[(size_t)q * k_out + t] = (double)e_dist[ke];
                 nns[(size_t)q * k_out + t] = e_id[ke];
+                if (probe_out) probe_out[(size_t)q * k_out + t] = (uint16_t)(ke / MK);  // probe rank of the entry
                 e_dist[ke] = __int_as_float(0x7fc00000);
             }
         }
@@ -212,11 +215,21 @@ __global__ void merge_topk_kernel(const float* __restrict__ part_sim, const int3
     }
 }
 
-// rank w's ascending lists live at d_all + w*stride_d / i_all + w*stride_i, each [nq, k];
-// output [nq, k]; ties keep the lower rank, then the lower position
+// Cross-rank key.  The unsharded search orders equal distances by (probe rank, position in the bucket's
+// top-10) -- the stable argsort over the rounds, LearnedIndex.py:131-134.  Inside one rank's list that order is
+// already in place; ACROSS ranks an equal distance is resolved by the entry's probe rank (carried per entry when
+// the caller passes it), then by the rank: whole-bucket sharding puts different probes on different ranks, and
+// row-slice sharding gives the lower rows of a bucket to the lower rank.  Without probe ranks: (distance, rank).
+__device__ __forceinline__ bool rank_key_less(double d0, int p0, int e0, double d1, int p1, int e1) {
+    return d0 < d1 || (d0 == d1 && (p0 < p1 || (p0 == p1 && e0 < e1)));
+}
+
+// rank w's ascending lists live at d_all + w*stride_d / i_all + w*stride_i (/ p_all + w*stride_p), each [nq, k];
+// output [nq, k]
 __global__ void merge_ranks_kernel(const double* __restrict__ d_all, const uint32_t* __restrict__ i_all,
-                                   int64_t stride_d, int64_t stride_i, int world, int nq, int k,
-                                   double* __restrict__ dists, uint32_t* __restrict__ nns) {
+                                   const uint16_t* __restrict__ p_all, int64_t stride_d, int64_t stride_i,
+                                   int64_t stride_p, int world, int nq, int k, double* __restrict__ dists,
+                                   uint32_t* __restrict__ nns) {
     const int warps = blockDim.x >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = blockIdx.x * warps + warp;
@@ -225,17 +238,22 @@ __global__ void merge_ranks_kernel(const double* __restrict__ d_all, const uint3
     int head = 0;
     const size_t base_d = (size_t)lane * stride_d + (size_t)q * k;
     const size_t base_i = (size_t)lane * stride_i + (size_t)q * k;
-    double hv = (lane < world) ? d_all[base_d] : INFINITY;
+    const size_t base_p = (size_t)lane * stride_p + (size_t)q * k;
     bool live = lane < world;
+    double hv = live ? d_all[base_d] : INFINITY;
+    int hp = (live && p_all) ? (int)p_all[base_p] : 0;
     for (int t = 0; t < k; ++t) {
         double kd = hv;
+        int kp = hp;
         int ke = live ? lane : 0x7fffffff;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const double od = __shfl_xor_sync(0xffffffffu, kd, o);
+            const int op = __shfl_xor_sync(0xffffffffu, kp, o);
             const int oe = __shfl_xor_sync(0xffffffffu, ke, o);
-            if (oe != 0x7fffffff && (ke == 0x7fffffff || od < kd || (od == kd && oe < ke))) {
+            if (oe != 0x7fffffff && (ke == 0x7fffffff || rank_key_less(od, op, oe, kd, kp, ke))) {
                 kd = od;
+                kp = op;
                 ke = oe;
             }
         }
@@ -250,18 +268,23 @@ __global__ void merge_ranks_kernel(const double* __restrict__ d_all, const uint3
             dists[(size_t)q * k + t] = hv;
             nns[(size_t)q * k + t] = i_all[base_i + head];
             ++head;
-            if (head < k) hv = d_all[base_d + head];
-            else live = false;
+            if (head < k) {
+                hv = d_all[base_d + head];
+                if (p_all) hp = (int)p_all[base_p + head];
+            } else {
+                live = false;
+            }
         }
     }
 }
 
-// The exchange step and the merge in ONE launch: rank w's packed block [dists f64[nq,k] | nns u32[nq,k]]
-// is read straight out of PEER memory (rank_base[w] is that rank's symmetric-memory buffer mapped into
-// this process: NVLink P2P loads through NVSwitch), staged per warp in shared memory with every lane
+// The exchange step and the merge in ONE launch: rank w's packed block [dists f64[nq,k] | nns u32[nq,k] |
+// probe u16[nq,k]] is read straight out of PEER memory (rank_base[w] is that rank's symmetric-memory buffer mapped
+// into this process: NVLink P2P loads through NVSwitch), staged per warp in shared memory with every lane
 // issuing independent remote loads, then merged as in merge_ranks_kernel.
-__global__ void merge_ranks_peer_kernel(const void* const* __restrict__ rank_base, int64_t nns_off, int world, int nq,
-                                        int k, double* __restrict__ dists, uint32_t* __restrict__ nns) {
+__global__ void merge_ranks_peer_kernel(const void* const* __restrict__ rank_base, int64_t nns_off, int64_t probe_off,
+                                        int world, int nq, int k, double* __restrict__ dists,
+                                        uint32_t* __restrict__ nns) {
     extern __shared__ double peer_sm[];
     const int warps = blockDim.x >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -270,25 +293,32 @@ __global__ void merge_ranks_peer_kernel(const void* const* __restrict__ rank_bas
     const int per = world * k;
     double* sd = peer_sm + (size_t)warp * per;
     uint32_t* si = reinterpret_cast<uint32_t*>(peer_sm + (size_t)warps * per) + (size_t)warp * per;
+    uint16_t* sp = reinterpret_cast<uint16_t*>(reinterpret_cast<uint32_t*>(peer_sm + (size_t)warps * per) +
+                                               (size_t)warps * per) + (size_t)warp * per;
     for (int idx = lane; idx < per; idx += 32) {
         const int w = idx / k, j = idx - w * k;
         const char* base = static_cast<const char*>(rank_base[w]);
         sd[idx] = reinterpret_cast<const double*>(base)[(size_t)q * k + j];
         si[idx] = reinterpret_cast<const uint32_t*>(base + nns_off)[(size_t)q * k + j];
+        sp[idx] = probe_off >= 0 ? reinterpret_cast<const uint16_t*>(base + probe_off)[(size_t)q * k + j] : (uint16_t)0;
     }
     __syncwarp();
     int head = 0;
     bool live = lane < world;
     double hv = live ? sd[lane * k] : INFINITY;
+    int hp = live ? (int)sp[lane * k] : 0;
     for (int t = 0; t < k; ++t) {
         double kd = hv;
+        int kp = hp;
         int ke = live ? lane : 0x7fffffff;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const double od = __shfl_xor_sync(0xffffffffu, kd, o);
+            const int op = __shfl_xor_sync(0xffffffffu, kp, o);
             const int oe = __shfl_xor_sync(0xffffffffu, ke, o);
-            if (oe != 0x7fffffff && (ke == 0x7fffffff || od < kd || (od == kd && oe < ke))) {
+            if (oe != 0x7fffffff && (ke == 0x7fffffff || rank_key_less(od, op, oe, kd, kp, ke))) {
                 kd = od;
+                kp = op;
                 ke = oe;
             }
         }
@@ -303,8 +333,12 @@ __global__ void merge_ranks_peer_kernel(const void* const* __restrict__ rank_bas
             dists[(size_t)q * k + t] = hv;
             nns[(size_t)q * k + t] = si[lane * k + head];
             ++head;
-            if (head < k) hv = sd[lane * k + head];
-            else live = false;
+            if (head < k) {
+                hv = sd[lane * k + head];
+                hp = (int)sp[lane * k + head];
+            } else {
+                live = false;
+            }
         }
     }
 }
@@ -325,13 +359,13 @@ __global__ void gather_peer_kernel(const void* const* __restrict__ rank_base, in
 extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, const int32_t* slot_of_pair,
                               const int32_t* bucket_order, const int64_t* bucket_off, const uint32_t* ids,
                               const int32_t* bucket_lists, int nq, int B, int C, int lmax, int k_out, double* dists,
-                              uint32_t* nns, void* stream) {
+                              uint32_t* nns, uint16_t* probe_rank, void* stream) {
     if (!part_sim || !part_row || !slot_of_pair || !bucket_order || !bucket_off || !ids || !bucket_lists || !dists ||
         !nns)
         return LMI_E_BADARG;
     if (nq < 0 || B <= 0 || C <= 0 || lmax <= 0 || k_out <= 0) return LMI_E_BADARG;
     if (k_out > B * lmi::MK) return LMI_E_BADARG;
-    if (lmax > 32 * lmi::MERGE_LPL) return LMI_E_UNSUPPORTED;
+    if (lmax > 32 * lmi::MERGE_LPL || B >= 0xffff) return LMI_E_UNSUPPORTED;
     if (nq == 0) return 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t per_warp = (size_t)2 * B * lmi::MK * sizeof(float);
@@ -346,33 +380,35 @@ extern "C" int lmi_merge_topk(const float* part_sim, const int32_t* part_row, co
     }
     const int grid = (nq + warps - 1) / warps;
     lmi::merge_topk_kernel<<<grid, warps * 32, smem, st>>>(part_sim, part_row, slot_of_pair, bucket_order, bucket_off,
-                                                           ids, bucket_lists, nq, B, C, lmax, k_out, dists, nns);
+                                                           ids, bucket_lists, nq, B, C, lmax, k_out, dists, nns,
+                                                           probe_rank);
     return static_cast<int>(cudaGetLastError());
 }
 
-extern "C" int lmi_merge_ranks(const double* dists_all, const uint32_t* nns_all, int64_t rank_stride_d,
-                               int64_t rank_stride_i, int world, int nq, int k, double* dists, uint32_t* nns,
-                               void* stream) {
+extern "C" int lmi_merge_ranks(const double* dists_all, const uint32_t* nns_all, const uint16_t* probe_all,
+                               int64_t rank_stride_d, int64_t rank_stride_i, int64_t rank_stride_p, int world, int nq,
+                               int k, double* dists, uint32_t* nns, void* stream) {
     if (!dists_all || !nns_all || !dists || !nns || world <= 0 || nq < 0 || k <= 0) return LMI_E_BADARG;
     if (world > 32) return LMI_E_UNSUPPORTED;
     if (nq == 0) return 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int warps = 4;
-    lmi::merge_ranks_kernel<<<(nq + warps - 1) / warps, warps * 32, 0, st>>>(dists_all, nns_all, rank_stride_d,
-                                                                           rank_stride_i, world, nq, k, dists, nns);
+    lmi::merge_ranks_kernel<<<(nq + warps - 1) / warps, warps * 32, 0, st>>>(
+        dists_all, nns_all, probe_all, rank_stride_d, rank_stride_i, rank_stride_p, world, nq, k, dists, nns);
     return static_cast<int>(cudaGetLastError());
 }
 
-extern "C" int lmi_merge_ranks_peer(const void* const* rank_base, int64_t nns_offset_bytes, int world, int nq, int k,
-                                    double* dists, uint32_t* nns, void* stream) {
+extern "C" int lmi_merge_ranks_peer(const void* const* rank_base, int64_t nns_offset_bytes, int64_t probe_offset_bytes,
+                                    int world, int nq, int k, double* dists, uint32_t* nns, void* stream) {
     if (!rank_base || !dists || !nns || world <= 0 || nq < 0 || k <= 0 || nns_offset_bytes < 0) return LMI_E_BADARG;
-    if (world > 32 || (nns_offset_bytes & 3)) return LMI_E_UNSUPPORTED;
+    if (world > 32 || (nns_offset_bytes & 3) || (probe_offset_bytes >= 0 && (probe_offset_bytes & 1)))
+        return LMI_E_UNSUPPORTED;
     if (nq == 0) return 0;
     const int warps = 4;
-    const size_t smem = (size_t)warps * world * k * (sizeof(double) + sizeof(uint32_t));
+    const size_t smem = (size_t)warps * world * k * (sizeof(double) + sizeof(uint32_t) + sizeof(uint16_t));
     if (smem > 48 * 1024) return LMI_E_UNSUPPORTED;
     lmi::merge_ranks_peer_kernel<<<(nq + warps - 1) / warps, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
-        rank_base, nns_offset_bytes, world, nq, k, dists, nns);
+        rank_base, nns_offset_bytes, probe_offset_bytes, world, nq, k, dists, nns);
     return static_cast<int>(cudaGetLastError());
 }
 

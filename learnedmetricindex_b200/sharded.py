@@ -53,20 +53,25 @@ def owner_of_bucket(parts: List[List[int]], n_buckets: int) -> np.ndarray:
 
 
 class GatherBuffers:
-    """Packed all-gather buffers: per rank ``[nq*k f64][nq*k u32]`` padded to 16 bytes."""
+    """Packed all-gather buffers: per rank ``[nq*k f64][nq*k u32][nq*k u16]`` padded to 16 bytes -- distances,
+    ids, and the probe rank of every entry (``lmi_merge_topk``'s ``probe_rank``), which the rank merge uses to
+    order equal distances exactly as the unsharded search does (zeros = absent: ties keep the lower rank)."""
 
     def __init__(self, nq: int, k: int, world: int, rank: int, device):
         self.nq, self.k, self.world, self.rank = nq, k, world, rank
         self.bytes_d = nq * k * 8
         self.bytes_i = nq * k * 4
-        self.per_rank = -(-(self.bytes_d + self.bytes_i) // 16) * 16
+        self.bytes_p = nq * k * 2
+        self.off_p = self.bytes_d + self.bytes_i
+        self.per_rank = -(-(self.off_p + self.bytes_p) // 16) * 16
         self.send = torch.zeros(self.per_rank, dtype=torch.uint8, device=device)
         self.recv = torch.zeros(self.per_rank * world, dtype=torch.uint8, device=device)
 
-    def local_views(self) -> Tuple[torch.Tensor, torch.Tensor]:
+    def local_views(self) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
         d = self.send[: self.bytes_d].view(torch.float64).view(self.nq, self.k)
         i = self.send[self.bytes_d : self.bytes_d + self.bytes_i].view(torch.int32).view(self.nq, self.k)
-        return d, i
+        p = self.send[self.off_p : self.off_p + self.bytes_p].view(torch.int16).view(self.nq, self.k)
+        return d, i, p
 
     def rank_views(self, w: int) -> Tuple[torch.Tensor, torch.Tensor]:
         base = w * self.per_rank
@@ -81,6 +86,10 @@ class GatherBuffers:
     @property
     def stride_i(self) -> int:
         return self.per_rank // 4
+
+    @property
+    def stride_p(self) -> int:
+        return self.per_rank // 2
 
 
 class PeerBuffers:
@@ -98,7 +107,9 @@ class PeerBuffers:
         self.nq, self.k, self.world, self.rank = nq, k, world, rank
         self.bytes_d = nq * k * 8
         self.bytes_i = nq * k * 4
-        self.per_rank = -(-(self.bytes_d + self.bytes_i) // 16) * 16
+        self.bytes_p = nq * k * 2  # probe rank of every entry: see GatherBuffers
+        self.off_p = self.bytes_d + self.bytes_i
+        self.per_rank = -(-(self.off_p + self.bytes_p) // 16) * 16
         self.blocks, self.handles = [], []
         for _ in range(n_blocks):  # a captured graph owns ONE block (fixed pointers); two graphs alternate instead
             t = symm_mem.empty(self.per_rank, dtype=torch.uint8, device=device)
@@ -107,11 +118,12 @@ class PeerBuffers:
             self.blocks.append(t)
         self.turn = 0
 
-    def local_views(self) -> Tuple[torch.Tensor, torch.Tensor]:
+    def local_views(self) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
         blk = self.blocks[self.turn]
         d = blk[: self.bytes_d].view(torch.float64).view(self.nq, self.k)
         i = blk[self.bytes_d : self.bytes_d + self.bytes_i].view(torch.int32).view(self.nq, self.k)
-        return d, i
+        p = blk[self.off_p : self.off_p + self.bytes_p].view(torch.int16).view(self.nq, self.k)
+        return d, i, p
 
     def exchange_and_merge(self, out=None):
         from . import _native
@@ -124,8 +136,8 @@ class PeerBuffers:
             out_d = torch.empty((self.nq, self.k), dtype=torch.float64, device=dev)
             out_i = torch.empty((self.nq, self.k), dtype=torch.int32, device=dev)
         hdl.barrier(channel=0)  # every rank's block of this turn is written (device-side, on this stream)
-        _native.check(_native.lib().lmi_merge_ranks_peer(hdl.buffer_ptrs_dev, self.bytes_d, self.world, self.nq,
-                                                         self.k, out_d.data_ptr(), out_i.data_ptr(),
+        _native.check(_native.lib().lmi_merge_ranks_peer(hdl.buffer_ptrs_dev, self.bytes_d, self.off_p, self.world,
+                                                         self.nq, self.k, out_d.data_ptr(), out_i.data_ptr(),
                                                          torch.cuda.current_stream().cuda_stream),
                       "lmi_merge_ranks_peer")
         self.turn = (self.turn + 1) % len(self.blocks)
@@ -179,8 +191,9 @@ def merge_ranks_device(buf: GatherBuffers, out_d: torch.Tensor, out_i: torch.Ten
 
     L = _native.lib()
     base = buf.recv.data_ptr()
-    _native.check(L.lmi_merge_ranks(base, base + buf.bytes_d, buf.stride_d, buf.stride_i, buf.world, buf.nq, buf.k,
-                                    out_d.data_ptr(), out_i.data_ptr(), torch.cuda.current_stream().cuda_stream),
+    _native.check(L.lmi_merge_ranks(base, base + buf.bytes_d, base + buf.off_p, buf.stride_d, buf.stride_i,
+                                    buf.stride_p, buf.world, buf.nq, buf.k, out_d.data_ptr(), out_i.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream),
                   "lmi_merge_ranks")
 
 

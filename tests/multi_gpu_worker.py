@@ -67,6 +67,28 @@ def main():
         assert torch.equal(d, exp_d), ("rows", B, k, rank)
         real = exp_d < 1e38
         assert torch.equal(i[real], exp_i[real]), ("rows ids", B, k, rank)
+    # exact distance ties ACROSS ranks: every vector exists twice, the copies live in neighbouring buckets (so mostly on
+    # different GPUs), and both copies of a near neighbour reach a query's top-k with the same f32 distance.  The rank
+    # merge must order them as the unsharded search does (by probe rank) -- bit-equal ids, not just equal distances
+    X2 = torch.cat([X, X]).numpy()
+    pred2 = np.concatenate([pred.numpy()[:, 0], (pred.numpy()[:, 0] + 1) % C])
+    full2 = DeviceBucketLayout.from_host(X2, pred2, C, device=dev)
+    parts2 = partition_buckets(np.diff(full2.bucket_off_host), world)
+    ref2 = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+    ref2.attach_layout(full2)
+    for B, k in [(4, 10), (6, 7)]:
+        exp_d, exp_i = ref2.search_device(Q, Q, [C], B, k)
+        ties = int((exp_d[:, 1:] == exp_d[:, :-1]).sum().item())
+        assert ties > nq // 4, f"the duplicated index should produce exact ties ({ties})"
+        for exchange in ("peer", "nccl"):
+            li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+            li.attach_layout(full2.restrict_to_buckets(parts2[rank]))
+            eng = ShardedLearnedIndex(li, exchange=exchange)
+            d, i = eng.search_device(Q, Q, [C], B, k)
+            assert torch.equal(d, exp_d) and torch.equal(i, exp_i), ("ties", exchange, B, k, rank)
+            if exchange == "peer":
+                dg, ig, _ = eng.search_graphed(Q, Q, [C], B, k)
+                assert torch.equal(dg, exp_d) and torch.equal(ig, exp_i), ("ties graph", B, k, rank)
     dist.barrier()
     if rank == 0:
         print("MULTI_GPU_OK", world)

@@ -249,3 +249,40 @@ def test_headline_size_matches_the_oracle_on_a_query_sample():
     parity = cb.explain(d_cpu, i_cpu, order_cpu, d, i, order_gpu)
     assert parity["queries"] == nq and parity["unexplained"] == 0, parity
     assert parity["bucket_order_rows_equal"] > 0.995 and parity["id_agreement"] > 0.999, parity
+
+
+def test_rank_merge_orders_equal_distances_by_probe_rank_then_gpu_rank():
+    """lmi_merge_ranks (after an all-gather) with the per-entry probe ranks lmi_merge_topk emits: equal distances
+    from different GPUs come out in (probe rank, GPU rank) order -- the single-GPU search's stable order over the
+    rounds (LearnedIndex.py:131-134) -- and without probe ranks in GPU-rank order."""
+    from learnedmetricindex_b200 import _native
+
+    L = _native.lib()
+    rs = np.random.RandomState(4)
+    world, nq, k = 4, 257, 10
+    # few distinct distance values -> many ties across ranks; every rank's list ascending in (dist, probe)
+    d = rs.randint(0, 6, size=(world, nq, k)).astype(np.float64) / 4.0
+    p = rs.randint(0, 5, size=(world, nq, k)).astype(np.uint16)
+    ids = rs.randint(1, 1 << 30, size=(world, nq, k)).astype(np.uint32)
+    for w in range(world):
+        for q in range(nq):
+            o = np.lexsort((p[w, q], d[w, q]))
+            d[w, q], p[w, q], ids[w, q] = d[w, q][o], p[w, q][o], ids[w, q][o]
+    dev = torch.device("cuda")
+    td, ti, tp = (torch.from_numpy(a).to(dev) for a in (d, ids.view(np.int32), p.view(np.int16)))
+    out_d = torch.empty((nq, k), dtype=torch.float64, device=dev)
+    out_i = torch.empty((nq, k), dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    for with_probe in (True, False):
+        _native.check(L.lmi_merge_ranks(td.data_ptr(), ti.data_ptr(), tp.data_ptr() if with_probe else None, nq * k,
+                                        nq * k, nq * k, world, nq, k, out_d.data_ptr(), out_i.data_ptr(), st))
+        torch.cuda.synchronize()
+        got_d, got_i = out_d.cpu().numpy(), out_i.cpu().numpy().view(np.uint32)
+        for q in range(nq):
+            fd = d[:, q].reshape(-1)
+            fp = p[:, q].reshape(-1).astype(np.int64) if with_probe else np.zeros(world * k, dtype=np.int64)
+            fr = np.repeat(np.arange(world), k)
+            fpos = np.tile(np.arange(k), world)
+            o = np.lexsort((fpos, fr, fp, fd))[:k]
+            np.testing.assert_array_equal(got_d[q], fd[o])
+            np.testing.assert_array_equal(got_i[q], ids[:, q].reshape(-1)[o])

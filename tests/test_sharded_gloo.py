@@ -83,7 +83,7 @@ def _worker(rank, world, port, B, k, ret):
                                 ids=ids[mine])
         kk = d.shape[1]
         buf = GatherBuffers(Q.shape[0], kk, world, rank, "cpu")
-        ld, li = buf.local_views()
+        ld, li, _ = buf.local_views()  # no probe ranks from the CPU oracle: ties keep the lower rank
         ld.copy_(torch.from_numpy(d))
         li.copy_(torch.from_numpy(i.view(np.int32)))
         out_d, out_i = gather_and_merge(buf, None, merge_fn=_numpy_merge)
