@@ -53,7 +53,7 @@
 extern "C" {
 #endif
 
-#define LMI_B200_ABI_VERSION 5
+#define LMI_B200_ABI_VERSION 6
 
 #define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
 #define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
@@ -194,7 +194,8 @@ int64_t lmi_invert_workspace_ints(int nq, int B, int C);
 #define LMI_WS_PART_SIM 8       /* f32[nq*B, 2*rmax, 10]  lmi_scan_topk part_sim   */
 #define LMI_WS_PART_ROW 9       /* int32[nq*B, 2*rmax, 10] lmi_scan_topk part_row  */
 #define LMI_WS_Q16 10           /* fp16[nq, d_pad]        cast / padded queries    */
-#define LMI_WS_ARRAYS 11
+#define LMI_WS_GATE 11          /* uint32[2*rmax, nq*B]   lmi_scan_topk gate       */
+#define LMI_WS_ARRAYS 12
 int64_t lmi_workspace_layout(int nq, int B, int C, int rmax, int d_pad, int64_t *offsets_host);
 int64_t lmi_workspace_bytes(int nq, int B, int C, int rmax);
 
@@ -220,8 +221,8 @@ int64_t lmi_workspace_bytes(int nq, int B, int C, int rmax);
  *                                   (= ranges of b x LMI_LISTS_PER_ITEM; 0 for an unprobed bucket)
  *   pair_list    int32[nq*B]   out  flat pair index per sorted slot
  *   slot_of_pair int32[nq*B]   out  inverse permutation (-1 for ignored pairs)
- *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, first list, bucket, query tile
- *                                   index within (bucket, range), query tiles of the bucket}
+ *   items        int32[max_items*8] out  {row0, nrows, slot0, mvalid, first list | lists of the bucket << 16,
+ *                                   bucket, query tile index within (bucket, range), query tiles of the bucket}
  *   n_items      int32[2]      out  [0] number of items; [1] = 0, the scan's item counter
  *   workspace    int32[lmi_invert_workspace_ints(nq,B,C)]  scratch
  */
@@ -242,13 +243,25 @@ int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t 
  *   part_sim  f32 [nq*B, lmax, 10] out  descending; -inf where fewer than 10 rows
  *   part_row  i32 [nq*B, lmax, 10] out  row index into X; -1 where empty
  * An item writes lists {first list, first list + 1} of each of its queries.
- * impl: 0 = tcgen05/TMA kernel (product path), 1 = plain CUDA-core verification
- * kernel (tests only; any d).
+ *   gate      uint32[lmax, nq*B] scratch, optional (NULL: off).  The row ranges of one bucket are scanned by
+ *             different CTAs at the same time, each keeping its own top-10 lists.  Through this array every list
+ *             publishes, per (query, bucket) pair, its j-th best similarity so far; when m lists hold j entries
+ *             above a value v and m*j >= 10, ten rows of the bucket beat v, so every list may skip scores below
+ *             the m-th largest published value ((j, m) = (2, 5) for a bucket of >= 5 lists, else (5, 2)).  The
+ *             partial lists then hold fewer entries below the final 10th best (and vary run to run); the merged
+ *             result is unchanged.  The call resets the array itself.
+ * impl (low 8 bits; every value gives bit-identical lists):
+ *   0 = tcgen05/TMA kernel, one CTA per work item, 64-row score tiles, two accumulators (product path)
+ *   1 = plain CUDA-core verification kernel (tests only; any d)
+ *   2 = the impl-0 kernel over thread-block clusters of two CTAs: two query tiles of one (bucket, range)
+ *       receive the bucket rows by ONE multicast TMA load (measured: not faster)
+ *   3 = 128-row score tiles (N = 128 MMAs, half the A-operand reads per flop), one accumulator
+ * impl >> 8: tuning flags (bit 0: L2 eviction hints by sibling order); results do not depend on them.
  */
 int lmi_scan_topk(const void *X, int64_t n, int d, const void *Q, int nq, int B,
                   const int32_t *pair_list, const int32_t *items, const int32_t *n_items,
                   int64_t max_items, int lmax, float *part_sim, int32_t *part_row,
-                  int impl, void *stream);
+                  int impl, uint32_t *gate, void *stream);
 
 /* ---- merge ------------------------------------------------------------------- */
 

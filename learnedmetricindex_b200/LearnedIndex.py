@@ -39,9 +39,9 @@ DEFAULT_RANGE_ROWS = 24576  # upper bound on the rows of a scan work item (see p
 DEFAULT_SCAN_IMPL = 0
 GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index (least recently used goes first)
 WS_CACHE = 8  # batch shapes whose workspace is kept
-WS_ARRAYS = 11  # LMI_WS_ARRAYS
+WS_ARRAYS = 12  # LMI_WS_ARRAYS
 (WS_COUNTS, WS_OFFSETS, WS_BUCKET_LISTS, WS_PAIR_LIST, WS_SLOT_OF_PAIR, WS_ITEMS, WS_N_ITEMS, WS_INVERT_SCRATCH,
- WS_PART_SIM, WS_PART_ROW, WS_Q16) = range(WS_ARRAYS)
+ WS_PART_SIM, WS_PART_ROW, WS_Q16, WS_GATE) = range(WS_ARRAYS)
 
 
 def _stream_ptr() -> int:
@@ -53,7 +53,7 @@ def _round_up(v: int, m: int) -> int:
 
 
 def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_bucket: int,
-              n_sms: int = 148, n_nonempty: Optional[int] = None) -> Dict[str, int]:
+              n_sms: int = 148, n_nonempty: Optional[int] = None, rows_per_tile: int = SCAN_ROWS_PER_TILE) -> Dict[str, int]:
     """How ``lmi_invert`` cuts the probed buckets into scan work items.
 
     Work items are (bucket, row range, tile of 128 probing queries), drawn in list order by the scan's
@@ -73,10 +73,10 @@ def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_b
     env = os.environ.get
     main = int(env("LMI_RANGE_ROWS", 0)) or int(min(DEFAULT_RANGE_ROWS, max(rows_per_sm / 6.0, 2048.0)))
     main = max(main, floor_rows)
-    main = _round_up(min(main, max(max_bucket, SCAN_ROWS_PER_TILE)), SCAN_ROWS_PER_TILE)
+    main = _round_up(min(main, max(max_bucket, rows_per_tile)), rows_per_tile)
     tail = int(env("LMI_TAIL_ROWS", 0)) or main // 3
     # keep every bucket within 16 ranges (= 32 partial lists per probe: the merge's one-list-per-lane path)
-    tail = _round_up(max(tail, floor_rows, -(-max_bucket // 16)), SCAN_ROWS_PER_TILE)
+    tail = _round_up(max(tail, floor_rows, -(-max_bucket // 16)), rows_per_tile)
     permille = env("LMI_TAIL_PERMILLE")
     if permille is not None:
         permille = int(permille)
@@ -94,12 +94,13 @@ class _BatchWorkspace:
     """Every transient array of one batch shape, in ONE allocation carved by ``lmi_workspace_layout``
     (SURVEY.md section 8b): a search allocates nothing but its two small result tensors."""
 
-    def __init__(self, lib, layout: DeviceBucketLayout, nq: int, B: int, n_sms: int, q_needs_copy: bool):
+    def __init__(self, lib, layout: DeviceBucketLayout, nq: int, B: int, n_sms: int, q_needs_copy: bool,
+                 rows_per_tile: int = SCAN_ROWS_PER_TILE):
         import ctypes
 
         self.nq, self.B = nq, B
         C = layout.n_buckets
-        self.plan = plan_scan(nq, B, C, layout.n, layout.max_bucket, n_sms, layout.n_nonempty)
+        self.plan = plan_scan(nq, B, C, layout.n, layout.max_bucket, n_sms, layout.n_nonempty, rows_per_tile)
         self.rmax = self.plan["rmax"]
         self.lmax = self.rmax * LISTS_PER_ITEM
         self.max_items = int(lib.lmi_max_items(nq, B, C, self.rmax))
@@ -127,8 +128,10 @@ class LearnedIndex:
         """Path -> internal model (multi-level indexes)."""
         self.bucket_paths = [tuple(p) for p in (bucket_paths or [])]
         """List of paths to the buckets."""
-        # lmi_scan_topk impl: 0 = tcgen05/TMA kernel, one CTA per work item; 2 = the same kernel over clusters of
-        # two CTAs that share bucket rows by TMA multicast; 1 = CUDA-core verification kernel (tests)
+        # lmi_scan_topk impl: 0 = tcgen05/TMA kernel, one CTA per work item, 64-row score tiles; 3 = the same with
+        # 128-row score tiles (one accumulator); 4 = 128-row tiles, two accumulators, the queries split between
+        # tensor memory and shared memory; 2 = 64-row tiles over clusters of two CTAs that share bucket rows by
+        # TMA multicast; 1 = CUDA-core verification kernel (tests)
         self.scan_impl = int(os.environ.get("LMI_SCAN_IMPL", DEFAULT_SCAN_IMPL)) if scan_impl is None else int(scan_impl)
         # The scan computes f32 arithmetic on fp16 values -- exactly the reference's arithmetic when the data is
         # fp16 on disk (SISAP `emb`).  f32 data that fp16 cannot represent is ROUNDED (2^-11 relative per
@@ -148,6 +151,8 @@ class LearnedIndex:
         self._warned_rounding = False
         self._n_sms = torch.cuda.get_device_properties(self.device).multi_processor_count
         self.scan_flags = int(os.environ.get("LMI_SCAN_FLAGS", "0"))  # lmi_scan_topk tuning flags (results identical)
+        # the ranges of a bucket share their running 10th-best through global memory (lmi_scan_topk's `gate`)
+        self.share_gate = os.environ.get("LMI_SCAN_SHARE_GATE", "1") != "0"
 
     @classmethod
     def from_reference(cls, li, **kw) -> "LearnedIndex":
@@ -260,7 +265,8 @@ class LearnedIndex:
         if ws is None:
             if len(self._workspaces) >= WS_CACHE:
                 self._workspaces.popitem(last=False)
-            ws = _BatchWorkspace(_native.lib(), self._layout, nq, B, self._n_sms, q_needs_copy)
+            ws = _BatchWorkspace(_native.lib(), self._layout, nq, B, self._n_sms, q_needs_copy,
+                                 128 if (self.scan_impl & 0xff) in (3, 4) else SCAN_ROWS_PER_TILE)
             self._workspaces[key] = ws
         else:
             self._workspaces.move_to_end(key)
@@ -339,7 +345,8 @@ class LearnedIndex:
         if layout.n > 0:
             _native.check(L.lmi_scan_topk(layout.vectors.data_ptr(), layout.n, layout.d, q16.data_ptr(), nq, B,
                                           P[WS_PAIR_LIST], P[WS_ITEMS], P[WS_N_ITEMS], ws.max_items, ws.lmax,
-                                          P[WS_PART_SIM], P[WS_PART_ROW], self.scan_impl | (self.scan_flags << 8), st),
+                                          P[WS_PART_SIM], P[WS_PART_ROW], self.scan_impl | (self.scan_flags << 8),
+                                          P[WS_GATE] if self.share_gate else None, st),
                           "lmi_scan_topk")
         mark(3)
         _native.check(L.lmi_merge_topk(P[WS_PART_SIM], P[WS_PART_ROW], P[WS_SLOT_OF_PAIR], order.data_ptr(),

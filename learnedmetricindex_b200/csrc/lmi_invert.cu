@@ -177,7 +177,7 @@ invert_scan_kernel(int32_t* __restrict__ hist, int C, int G, const int64_t* __re
                 if (idx >= max_items) continue;
                 int4* dst = reinterpret_cast<int4*>(items + idx * LMI_ITEM_WORDS);
                 dst[0] = make_int4((int)row0, nrows, off + t * SCAN_M_TILE, min(SCAN_M_TILE, m - t * SCAN_M_TILE));
-                dst[1] = make_int4(r * LMI_LISTS_PER_ITEM, c, t, nt);
+                dst[1] = make_int4(r * LMI_LISTS_PER_ITEM | (nr * LMI_LISTS_PER_ITEM) << 16, c, t, nt);
             }
         }
         __syncthreads();
@@ -261,6 +261,7 @@ extern "C" int64_t lmi_workspace_layout(int nq, int B, int C, int rmax, int d_pa
         4LL * lists,                                        // LMI_WS_PART_SIM
         4LL * lists,                                        // LMI_WS_PART_ROW
         2LL * nq * d_pad,                                   // LMI_WS_Q16
+        4LL * P * rmax * LMI_LISTS_PER_ITEM,                // LMI_WS_GATE
     };
     int64_t at = 0;
     for (int i = 0; i < LMI_WS_ARRAYS; ++i) {

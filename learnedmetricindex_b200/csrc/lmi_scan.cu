@@ -47,17 +47,27 @@ constexpr int SCAN_MAX_D = 768;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t TMEM_ACC_COL = SCAN_MAX_D / 2;  // A: columns [0,384); accumulators: [384,448), [448,512)
 constexpr int TOPK = LMI_PER_BUCKET_K;
+constexpr int SCAN_SPLIT_KT = 8;       // SPLIT arrangement: k-blocks of the queries in TMEM (the rest in shared memory)
+constexpr int SCAN_SPLIT_STAGES = 5;
+constexpr int SCAN_SPLIT_A_BYTES = (SCAN_MAX_D / SCAN_KBLK - SCAN_SPLIT_KT) * SCAN_M * 128;  // 64 KB
 constexpr int SCAN_SCHED_SLOTS = 4;   // item indices the producer may run ahead of the consumers
 constexpr size_t SCAN_SMEM_BYTES = (size_t)SCAN_STAGES * SCAN_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ +
                                    2 * SCAN_M * sizeof(float) /*gates*/;
+constexpr size_t SCAN_SPLIT_SMEM_BYTES = SCAN_SMEM_BYTES - (size_t)SCAN_STAGES * SCAN_STAGE_BYTES +
+                                         (size_t)SCAN_SPLIT_STAGES * SCAN_STAGE_BYTES + SCAN_SPLIT_A_BYTES;
+static_assert(SCAN_SPLIT_SMEM_BYTES <= 232448, "exceeds the 227 KB of dynamic shared memory per CTA");
 
 // Scan tuning flags (lmi_scan_topk's `impl` >> 8): results are identical for every value.
 constexpr int SCAN_FLAG_L2_SIBLINGS = 1;  // L2 eviction hints by sibling order (see the producer)
+// (tried and dropped: requesting tile t + 2..4 into L2 with cp.async.bulk.prefetch.tensor while tile t is loaded --
+// +14 % scan time at 10M, profiles/r02_scan_lab.md)
 
 #ifdef LMI_PROFILE
 // profiling build only (tools/): `dbg` ablations give WRONG results and are compiled out of the product
 // (dbg & 1: no TMA loads; & 2: no candidate processing; & 4: half the operand traffic; & 8: MMA-warp
-// wait cycles per CTA into g_scan_prof)
+// wait cycles per CTA into g_scan_prof; & 16: stages pre-filled with pseudo-random fp16, so that MMAs
+// without loads multiply real data -- zeros draw far less power; & 32: every load reads a 50 MB window,
+// i.e. L2 -> SM traffic as usual but nothing from HBM)
 __device__ long long g_scan_prof[148 * 8];
 #define LMI_DBG(x) (x)
 #else
@@ -66,6 +76,7 @@ __device__ long long g_scan_prof[148 * 8];
 
 struct ScanBarriers {
     uint64_t full[SCAN_STAGES];
+    uint64_t full_b[SCAN_STAGES];  // SPLIT: the second issuer's "stage filled" barriers
     uint64_t empty[SCAN_STAGES];
     uint64_t acc_full[2];
     uint64_t acc_empty[2];
@@ -118,14 +129,56 @@ __device__ __forceinline__ void store_topk(const TopK& tk, float* __restrict__ p
     }
 }
 
+// NT = bucket rows per score tile (= N of the MMA).  NT = 64: two accumulator buffers of 64 columns, two issuer
+// warps that alternate by tile (the layout described above).  NT = 128: K = 768 of queries fills 384 of the 512
+// tensor-memory columns, so ONE accumulator of 128 columns is left -- the tensor pipe pauses while the epilogue
+// warps pull a finished tile out of TMEM (the candidate processing itself overlaps the next tile) -- but every
+// MMA reads the A operand (4 KB of queries out of TMEM) for twice as many outputs, and one issuer warp suffices
+// (an N = 128 instruction lasts 64 cycles).  Same work items, same partial lists (column half h of a tile ->
+// list h), bit-identical results.
+// order-preserving float <-> uint32 (0 is below every float), so that bounds can be compared as integers
+__device__ __forceinline__ uint32_t gate_encode(float f) {
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float gate_decode(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <int NT, bool SPLIT>
 __global__ void __launch_bounds__(SCAN_THREADS, 1)
 scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __restrict__ Q,
                     const int32_t* __restrict__ pair_list, int B, const int32_t* __restrict__ items,
                     const int32_t* __restrict__ n_items_ptr, int64_t max_items, int d, int lmax,
-                    float* __restrict__ part_sim, int32_t* __restrict__ part_row, int flags, int dbg) {
+                    float* __restrict__ part_sim, int32_t* __restrict__ part_row, uint32_t* __restrict__ gate_g,
+                    size_t gate_stride, int flags, int dbg) {
+    constexpr int SCAN_N = NT;
+    constexpr int SCAN_BOX_BYTES = NT * 128;                    // one TMA box: NT rows x 64 fp16
+    constexpr int SCAN_BOXES = SCAN_STAGE_BYTES / SCAN_BOX_BYTES;  // k-blocks per 32 KB stage: 4 (NT = 64) / 2 (NT = 128)
+    // SPLIT (NT = 128 only): the queries' first KT = 8 k-blocks (512 dimensions, 256 columns) live in tensor memory
+    // and the remaining <= 4 k-blocks in shared memory (64 KB, the UMMA SWIZZLE_128B K-major layout, written by the
+    // gather) -- their MMAs take A from a shared-memory descriptor -- which leaves 256 columns for TWO accumulators
+    // of 128, so N = 128 tiles are double buffered like the N = 64 ones; the ring shrinks to 5 stages.
+    static_assert(!SPLIT || NT == 128, "SPLIT is the NT = 128 arrangement");
+    constexpr int NACC = (NT == 64 || SPLIT) ? 2 : 1;           // accumulator buffers that fit beside the queries
+    constexpr int ISSUERS = (NT == 64 || SPLIT) ? 2 : 1;        // issuer warps in use (they alternate by tile)
+    constexpr int HCOLS = NT / 2;                               // columns of a tile one epilogue warp owns
+    constexpr int KT = SPLIT ? SCAN_SPLIT_KT : SCAN_MAX_D / SCAN_KBLK;  // k-blocks of the queries held in TMEM
+    constexpr uint32_t ACC_COL = KT * (SCAN_KBLK / 2);          // first accumulator column
+    constexpr int NSTAGES = SPLIT ? SCAN_SPLIT_STAGES : SCAN_STAGES;
+    constexpr int A_S_BYTES = SPLIT ? SCAN_SPLIT_A_BYTES : 0;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    ScanBarriers* bars = reinterpret_cast<ScanBarriers*>(stages + (size_t)SCAN_STAGES * SCAN_STAGE_BYTES);
+    uint8_t* a_s = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* stages = a_s + A_S_BYTES;
+    ScanBarriers* bars = reinterpret_cast<ScanBarriers*>(stages + (size_t)NSTAGES * SCAN_STAGE_BYTES);
     float* gates = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // [2 halves][128 rows]
 
     const int warp = threadIdx.x >> 5;
@@ -153,8 +206,9 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
 
     if (warp == TMA_WARP && lane == 0) {
         ptx::tma_prefetch_desc(&tmap);
-        for (int s = 0; s < SCAN_STAGES; ++s) {
+        for (int s = 0; s < NSTAGES; ++s) {
             ptx::mbar_init(&bars->full[s], 1);
+            ptx::mbar_init(&bars->full_b[s], 1);
             ptx::mbar_init(&bars->empty[s], 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -164,7 +218,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         ptx::mbar_init(&bars->q_ready, SCAN_EPI_WARPS * 32);
         for (int b = 0; b < SCAN_SCHED_SLOTS; ++b) {
             ptx::mbar_init(&bars->sched_full[b], 1);
-            ptx::mbar_init(&bars->sched_empty[b], SCAN_EPI_WARPS + SCAN_MMA_WARPS);
+            ptx::mbar_init(&bars->sched_empty[b], SCAN_EPI_WARPS + ISSUERS);
         }
         ptx::fence_barrier_init();
     }
@@ -172,6 +226,16 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         ptx::tmem_alloc(&bars->tmem_base, TMEM_COLS);
         ptx::tmem_relinquish();
     }
+#ifdef LMI_PROFILE
+    if (dbg & 16) {  // ablation support: pseudo-random fp16 (|x| < 0.06) in every stage, so MMAs without loads see real data
+        for (int i = threadIdx.x; i < NSTAGES * SCAN_STAGE_BYTES / 4; i += SCAN_THREADS) {
+            uint32_t x = (uint32_t)i * 2654435761u + blockIdx.x * 40503u;
+            x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+            reinterpret_cast<uint32_t*>(stages)[i] = (x & 0x83ff83ffu) | 0x28002800u;
+        }
+        ptx::fence_proxy_async();
+    }
+#endif
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -189,7 +253,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         const uint64_t pol_keep = ptx::policy_evict_last();
         const uint64_t pol_drop = ptx::policy_evict_first();
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;  // stages per 64-row tile
-        uint32_t stage = 0, phase = 0, sslot = 0, sphase = 0;
+        uint32_t stage = 0, phase = 0, sslot = 0, sphase = 0, ptile = 0;
         while (true) {
             ptx::mbar_wait(&bars->sched_empty[sslot], sphase ^ 1);
             int it = 0;
@@ -211,7 +275,10 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
             uint64_t policy = pol_normal;
             if ((flags & SCAN_FLAG_L2_SIBLINGS) && w1.w > 1) policy = (w1.z + 1 == w1.w) ? pol_drop : pol_keep;
-            for (int t = 0; t < ntiles; ++t) {
+            for (int t = 0; t < ntiles; ++t, ++ptile) {
+                // SPLIT: a tile spans more stages than the ring holds, so a stage serves both issuers in turn; each
+                // issuer has its own "filled" barrier per stage (it then sees every phase of the barriers it waits on)
+                uint64_t* full_bars = (SPLIT && (ptile & 1)) ? bars->full_b : bars->full;
                 for (int s = 0; s < SPT; ++s) {
                     const int kb0 = s * SCAN_BOXES;
                     int nb = min(SCAN_BOXES, KB - kb0);
@@ -219,18 +286,20 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     if (ptx::elect_one()) {
                         uint8_t* dst = stages + (size_t)stage * SCAN_STAGE_BYTES;
                         if (LMI_DBG(dbg & 1)) {  // ablation: no loads, the MMAs run on whatever the stage holds
-                            ptx::mbar_arrive(&bars->full[stage]);
+                            ptx::mbar_arrive(&full_bars[stage]);
                             nb = 0;
                         } else {
                             if (LMI_DBG(dbg & 4)) nb = (nb + 1) / 2;  // ablation: half the operand traffic
-                            ptx::mbar_arrive_expect_tx(&bars->full[stage], nb * SCAN_BOX_BYTES);
+                            ptx::mbar_arrive_expect_tx(&full_bars[stage], nb * SCAN_BOX_BYTES);
                         }
+                        int trow = row0 + t * SCAN_N;
+                        if (LMI_DBG(dbg & 32)) trow &= 32767;  // ablation: every load hits a 50 MB window (L2, no HBM)
                         for (int b = 0; b < nb; ++b)
-                            ptx::tma_load_2d(dst + b * SCAN_BOX_BYTES, &tmap, (kb0 + b) * SCAN_KBLK, row0 + t * SCAN_N,
-                                             &bars->full[stage], policy);
+                            ptx::tma_load_2d(dst + b * SCAN_BOX_BYTES, &tmap, (kb0 + b) * SCAN_KBLK, trow,
+                                             &full_bars[stage], policy);
                     }
                     __syncwarp();
-                    if (++stage == SCAN_STAGES) {
+                    if (++stage == NSTAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
@@ -246,20 +315,25 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         // (tile counter & 1) == w, i.e. accumulator buffer w and every other group of SPT
         // pipeline stages, and does its barrier waits while the other warp is issuing.
         const uint32_t mw = warp - MMA_WARP;
+        if (mw >= (uint32_t)ISSUERS) goto done;  // NT = 128: one issuer
         constexpr uint32_t idesc = ptx::umma_idesc_f16(SCAN_M, SCAN_N);
         const int SPT = (KB + SCAN_BOXES - 1) / SCAN_BOXES;
         const uint64_t desc0 = ptx::umma_desc_sw128_kmajor(ptx::smem_u32(stages));
         const uint32_t desc0_lo = (uint32_t)desc0;
-        const uint64_t desc0_hi = desc0 >> 32;
+        const uint64_t desc0_hi = desc0 >> 32;  // the same for every SWIZZLE_128B K-major operand
+        const uint32_t descA_lo = (uint32_t)ptx::umma_desc_sw128_kmajor(ptx::smem_u32(a_s));
+        (void)descA_lo;
         uint32_t stage = 0, phase = 0, tcount = 0, item_parity = 0, sslot = 0, sphase = 0;
+        uint32_t use_bits = 0;  // SPLIT: bit s = parity of this issuer's uses of stage s so far
+        uint64_t* full_bars = (SPLIT && mw == 1) ? bars->full_b : bars->full;
         auto skip_tile_stages = [&]() {
             for (int s = 0; s < SPT; ++s)
-                if (++stage == SCAN_STAGES) {
+                if (++stage == NSTAGES) {
                     stage = 0;
                     phase ^= 1;
                 }
         };
-        if (mw == 1) skip_tile_stages();
+        if (ISSUERS == 2 && mw == 1) skip_tile_stages();
 #ifdef LMI_PROFILE
         const bool prof = (dbg & 8) != 0 && mw == 0;
         long long p_sched = 0, p_q = 0, p_acc = 0, p_full = 0, p_issue = 0, p_n = 0, p_t0 = clock64(), p_c;
@@ -285,19 +359,20 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             item_parity ^= 1;
             ptx::tc_fence_after();
             for (int t = 0; t < ntiles; ++t, ++tcount) {
-                const uint32_t buf = tcount & 1;
-                if (buf != mw) continue;
+                const uint32_t buf = tcount & (NACC - 1);
+                if (ISSUERS == 2 && buf != mw) continue;
                 PROF_BEGIN();
-                ptx::mbar_wait(&bars->acc_empty[buf], ((tcount >> 1) & 1) ^ 1);
+                ptx::mbar_wait(&bars->acc_empty[buf], ((tcount / NACC) & 1) ^ 1);
                 PROF_END(p_acc);
                 ptx::tc_fence_after();
-                const uint32_t d_tmem = tmem + TMEM_ACC_COL + buf * SCAN_N;
+                const uint32_t d_tmem = tmem + ACC_COL + buf * SCAN_N;
                 for (int s = 0; s < SPT; ++s) {
                     const int kb0 = s * SCAN_BOXES;
                     const int nb = min(SCAN_BOXES, KB - kb0);
                     PROF_BEGIN();
-                    ptx::mbar_wait(&bars->full[stage], phase);
+                    ptx::mbar_wait(&full_bars[stage], SPLIT ? ((use_bits >> stage) & 1u) : phase);
                     PROF_END(p_full);
+                    use_bits ^= 1u << stage;
                     ptx::tc_fence_after();
                     PROF_BEGIN();
                     PROF_COUNT();
@@ -308,7 +383,21 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                         // by compile-time constants (no dependent address arithmetic between them).
                         const uint32_t dlo = desc0_lo + ((stage * SCAN_STAGE_BYTES) >> 4);
                         const uint32_t a0 = tmem + kb0 * (SCAN_KBLK / 2);
-                        if (nb == SCAN_BOXES) {
+                        if (SPLIT && kb0 >= KT) {
+                            // the k-blocks of the queries that live in shared memory (KT is a multiple of the
+                            // boxes per stage, so a stage is all-TMEM or all-shared): A by descriptor
+                            const uint32_t alo = descA_lo + (((kb0 - KT) * (SCAN_M * 128)) >> 4);
+                            for (int b = 0; b < nb; ++b) {
+#pragma unroll
+                                for (int k = 0; k < SCAN_KBLK / 16; ++k) {
+                                    const uint64_t b_desc =
+                                        (desc0_hi << 32) | (uint64_t)(dlo + ((b * SCAN_BOX_BYTES + k * 32) >> 4));
+                                    const uint64_t a_desc =
+                                        (desc0_hi << 32) | (uint64_t)(alo + ((b * (SCAN_M * 128) + k * 32) >> 4));
+                                    ptx::mma_f16_ss(d_tmem, a_desc, b_desc, idesc, 1u);  // never a tile's first MMA (KT > 0)
+                                }
+                            }
+                        } else if (nb == SCAN_BOXES) {
 #pragma unroll
                             for (int b = 0; b < SCAN_BOXES; ++b) {
 #pragma unroll
@@ -335,12 +424,12 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     }
                     __syncwarp();
                     PROF_END(p_issue);
-                    if (++stage == SCAN_STAGES) {
+                    if (++stage == NSTAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                skip_tile_stages();  // the other issuer's tile
+                if (ISSUERS == 2) skip_tile_stages();  // the other issuer's tile
             }
         }
 #ifdef LMI_PROFILE
@@ -370,7 +459,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             if (it < 0) break;
             const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
             const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
-            const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
+            const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x & 0xffff;
             const int ntiles = (nrows + SCAN_N - 1) / SCAN_N;
             const bool valid = row < mvalid;
 
@@ -395,21 +484,36 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                     for (int v = 0; v < 32; ++v) r[v] = 0u;
                 }
             };
+            // k-block c of the row: into TMEM columns [32c, 32c + 32) of the row's lane, or (SPLIT, c >= KT) into the
+            // shared-memory A tile of k-block c - KT: row r of a 128-row SWIZZLE_128B K-major tile lies at
+            // (r / 8) * 1024 + (r % 8) * 128 and its 16-byte chunk j at position j ^ (r % 8)
+            auto store_kblock = [&](const uint32_t (&r)[32], int c) {
+                if (!SPLIT || c < KT) {
+                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), r);
+                } else {
+                    uint8_t* dst = a_s + (size_t)(c - KT) * (SCAN_M * 128) + (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<uint4*>(dst + ((j ^ (row & 7)) << 4)) =
+                            make_uint4(r[4 * j + 0], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                }
+            };
             {
                 uint32_t ra[32], rb[32];
                 int c = h;
                 if (c < KB) load_kblock(ra, c);
                 while (c < KB) {
                     if (c + 2 < KB) load_kblock(rb, c + 2);
-                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), ra);
+                    store_kblock(ra, c);
                     c += 2;
                     if (c >= KB) break;
                     if (c + 2 < KB) load_kblock(ra, c + 2);
-                    ptx::tmem_st32(tmem + lane_field + c * (SCAN_KBLK / 2), rb);
+                    store_kblock(rb, c);
                     c += 2;
                 }
             }
             ptx::tmem_st_wait();
+            if (SPLIT) ptx::fence_proxy_async();  // the shared-memory part is read by the tensor core (async proxy)
             *gate_mine = -INFINITY;
             ptx::tc_fence_before();
             ptx::mbar_arrive(&bars->q_ready);
@@ -417,40 +521,83 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
             TopK tk;
             tk.reset();
             float tau = -INFINITY;  // gate: a lower bound of this (row, range)'s final 10th best
+            // The (query, bucket) pair's gate shared with the CTAs scanning the bucket's other row ranges: list l of
+            // the pair publishes its GJ-th best so far in gate_g[l * pairs + slot]; GM lists with GJ entries above
+            // a value v (GM * GJ >= 10) mean ten rows of the bucket beat v, so the GM-th largest published value
+            // is a lower bound of the bucket's final 10th best.
+            const int n_lists = (w1.x >> 16) & 0xffff;
+            const bool wide = n_lists >= 5;  // (GJ, GM) = (2, 5), else (5, 2)
+            uint32_t* gate_pair = (gate_g != nullptr && valid && n_lists >= 2) ? gate_g + slot0 + row : nullptr;
+            uint32_t gate_pub = 0;  // what this list last published
             for (int t = 0; t < ntiles; ++t, ++tcount) {
-                const uint32_t buf = tcount & 1;
-                ptx::mbar_wait(&bars->acc_full[buf], (tcount >> 1) & 1);
+                const uint32_t buf = tcount & (NACC - 1);
+                // refresh the bound at tiles 1, 3, 7, 15, 23, ...: the loads are in flight while the tile is awaited
+                uint32_t gq = 0;
+                if (gate_pair != nullptr && (t == 1 || t == 3 || (t & 7) == 7)) {
+                    uint32_t top[5] = {0u, 0u, 0u, 0u, 0u};  // descending
+                    for (int l0 = 0; l0 < n_lists; l0 += 8) {
+                        uint32_t u[8];  // eight independent loads in flight, then the insertion network
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            u[i] = l0 + i < n_lists ? ld_relaxed_u32(gate_pair + (size_t)(l0 + i) * gate_stride) : 0u;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+#pragma unroll
+                            for (int e = 0; e < 5; ++e) {
+                                const uint32_t hi = max(top[e], u[i]);
+                                u[i] = min(top[e], u[i]);
+                                top[e] = hi;
+                            }
+                        }
+                    }
+                    gq = wide ? top[4] : top[1];
+                }
+                ptx::mbar_wait(&bars->acc_full[buf], (tcount / NACC) & 1);
                 ptx::tc_fence_after();
-                uint32_t v[32];
-                ptx::tmem_ld32(tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N + h * 32, v);
+                uint32_t v[HCOLS];
+                {
+                    uint32_t(&v0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
+                    ptx::tmem_ld32(tmem + lane_field + ACC_COL + buf * SCAN_N + h * HCOLS, v0);
+                    if (HCOLS == 64) {
+                        uint32_t(&v1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[HCOLS - 32]);
+                        ptx::tmem_ld32(tmem + lane_field + ACC_COL + buf * SCAN_N + h * HCOLS + 32, v1);
+                    }
+                }
                 // the other half's 10th best, nudged down so that an exact tie with it still
                 // reaches the (similarity, row)-keyed merge
                 const float og = *gate_other;
                 tau = fmaxf(tau, og - fabsf(og) * 2.4e-7f);
+                if (gq != 0u) {  // same nudge: an exact tie with the bound still reaches the merge
+                    const float gg = gate_decode(gq);
+                    tau = fmaxf(tau, gg - fabsf(gg) * 2.4e-7f);
+                }
                 ptx::tmem_ld_wait();
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&bars->acc_empty[buf]);  // scores are in registers now
 
-                const int base_row = row0 + t * SCAN_N + h * 32;
-                const int lim = nrows - t * SCAN_N - h * 32;  // columns of this half inside the range
-                if (lim < 32) {
+                const int base_row = row0 + t * SCAN_N + h * HCOLS;
+                const int lim = nrows - t * SCAN_N - h * HCOLS;  // columns of this half inside the range
+                if (lim < HCOLS) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
+                    for (int j = 0; j < HCOLS; ++j)
                         if (j >= lim) v[j] = 0xff800000u;  // -inf
                 }
-                float g[4];
+                constexpr int NG = HCOLS / 8;  // groups of 8 columns
+                float g[NG];
 #pragma unroll
-                for (int gi = 0; gi < 4; ++gi) {
+                for (int gi = 0; gi < NG; ++gi) {
                     float m = __uint_as_float(v[gi * 8]);
 #pragma unroll
                     for (int j = 1; j < 8; ++j) m = fmaxf(m, __uint_as_float(v[gi * 8 + j]));
                     g[gi] = m;
                 }
-                const float mall = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
+                float mall = g[0];
+#pragma unroll
+                for (int gi = 1; gi < NG; ++gi) mall = fmaxf(mall, g[gi]);
                 if (!LMI_DBG(dbg & 2) && __any_sync(0xffffffffu, mall > tau)) {
 #pragma unroll
-                    for (int gi = 0; gi < 4; ++gi) {
+                    for (int gi = 0; gi < NG; ++gi) {
                         if (__any_sync(0xffffffffu, g[gi] > tau)) {
                             uint32_t mask = 0;
 #pragma unroll
@@ -478,6 +625,14 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                         }
                     }
                     *gate_mine = tk.s[TOPK - 1];
+                    if (gate_pair != nullptr) {
+                        const float jth = wide ? tk.s[1] : tk.s[4];
+                        const uint32_t mine = jth > -INFINITY ? gate_encode(jth) : 0u;
+                        if (mine > gate_pub) {
+                            gate_pub = mine;
+                            st_relaxed_u32(gate_pair + (size_t)(list0 + h) * gate_stride, mine);
+                        }
+                    }
                 }
             }
             if (valid)
@@ -485,6 +640,7 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
         }
     }
 
+done:
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == MMA_WARP) {
@@ -599,7 +755,7 @@ scan_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __
             const int2 pw = *reinterpret_cast<const int2*>(items + (size_t)it_peer * LMI_ITEM_WORDS);
             shared = pw.x == w0.x && pw.y == w0.y;  // same rows: two query tiles of one (bucket, range)
         }
-        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
+        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x & 0xffff;
         const int ntiles = has ? (nrows + SCAN_N - 1) / SCAN_N : 0;
 
         if (warp == TMA_WARP) {
@@ -838,7 +994,7 @@ scan_topk_simt_kernel(const __half* __restrict__ X, const __half* __restrict__ Q
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const int4 w0 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS);
         const int4 w1 = *reinterpret_cast<const int4*>(items + (size_t)it * LMI_ITEM_WORDS + 4);
-        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x;
+        const int row0 = w0.x, nrows = w0.y, slot0 = w0.z, mvalid = w0.w, list0 = w1.x & 0xffff;
         const int row = threadIdx.x;
         const bool valid = row < mvalid;
         const int q = valid ? (pair_list[slot0 + row] / B) : 0;
@@ -891,7 +1047,7 @@ extern "C" int lmi_debug_scan_profile(long long* host_out /* [148*8] */) {
 extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int nq, int B,
                              const int32_t* pair_list, const int32_t* items, const int32_t* n_items,
                              int64_t max_items, int lmax, float* part_sim, int32_t* part_row, int impl,
-                             void* stream) {
+                             uint32_t* gate, void* stream) {
     if (!X || !Q || !pair_list || !items || !n_items || !part_sim || !part_row) return LMI_E_BADARG;
     if (n <= 0 || d <= 0 || nq <= 0 || B <= 0 || lmax <= 0 || max_items <= 0) return LMI_E_BADARG;
     if (n > 0x7fffffffLL) return LMI_E_UNSUPPORTED;
@@ -910,7 +1066,7 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
             lmax, part_sim, part_row);
         return static_cast<int>(cudaGetLastError());
     }
-    if (impl != 0 && impl != 2) return LMI_E_BADARG;
+    if (impl != 0 && impl != 2 && impl != 3 && impl != 4) return LMI_E_BADARG;  // 3 / 4: 128-row score tiles
     if (d % lmi::SCAN_KBLK != 0 || d > lmi::SCAN_MAX_D) return LMI_E_UNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(X) & 15) != 0 || (reinterpret_cast<uintptr_t>(Q) & 15) != 0) return LMI_E_BADARG;
 
@@ -919,7 +1075,7 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)n};
     const cuuint64_t gstride[1] = {(cuuint64_t)d * sizeof(__half)};
-    const cuuint32_t box[2] = {(cuuint32_t)lmi::SCAN_KBLK, (cuuint32_t)lmi::SCAN_N};
+    const cuuint32_t box[2] = {(cuuint32_t)lmi::SCAN_KBLK, (cuuint32_t)(impl >= 3 ? 128 : lmi::SCAN_N)};
     const cuuint32_t estride[2] = {1, 1};
     CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(X), gdim, gstride, box, estride,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -929,8 +1085,14 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
     // the opt-in to > 48 KB of dynamic shared memory is per device (context): remember it per device id
     static bool attr_set[64] = {};
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(lmi::scan_topk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)lmi::SCAN_SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(lmi::scan_topk_tc_kernel<64, false>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lmi::SCAN_SMEM_BYTES);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lmi::scan_topk_tc_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)lmi::SCAN_SMEM_BYTES);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lmi::scan_topk_tc_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)lmi::SCAN_SPLIT_SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
@@ -960,8 +1122,21 @@ extern "C" int lmi_scan_topk(const void* X, int64_t n, int d, const void* Q, int
 #endif
     cudaError_t me = cudaMemsetAsync(const_cast<int32_t*>(n_items) + 1, 0, sizeof(int32_t), st);  // scheduler counter
     if (me != cudaSuccess) return (int)me;
-    lmi::scan_topk_tc_kernel<<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
-        tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row, flags,
-        dbg);
+    if (gate != nullptr) {
+        me = cudaMemsetAsync(gate, 0, sizeof(uint32_t) * (size_t)nq * B * lmax, st);  // 0 = below every similarity
+        if (me != cudaSuccess) return (int)me;
+    }
+    if (impl == 4)
+        lmi::scan_topk_tc_kernel<128, true><<<grid, lmi::SCAN_THREADS, lmi::SCAN_SPLIT_SMEM_BYTES, st>>>(
+            tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row,
+            gate, (size_t)nq * B, flags, dbg);
+    else if (impl == 3)
+        lmi::scan_topk_tc_kernel<128, false><<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
+            tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row,
+            gate, (size_t)nq * B, flags, dbg);
+    else
+        lmi::scan_topk_tc_kernel<64, false><<<grid, lmi::SCAN_THREADS, lmi::SCAN_SMEM_BYTES, st>>>(
+            tmap, static_cast<const __half*>(Q), pair_list, B, items, n_items, max_items, d, lmax, part_sim, part_row,
+            gate, (size_t)nq * B, flags, dbg);
     return static_cast<int>(cudaGetLastError());
 }

@@ -24,16 +24,17 @@ def test_library_builds_loads_and_exports_header_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/lmi_b200.h but not exported"
     assert set(declared) == set(_native.EXPORTED_SYMBOLS), "ctypes signatures out of sync with the header"
-    assert lib.lmi_version() == 5
+    assert lib.lmi_version() == 6
     assert lib.lmi_error_string(0) == b"success"
     assert b"bad argument" in lib.lmi_error_string(-1)
     # size helpers are pure host functions
     assert lib.lmi_max_items(10000, 4, 120, 5) >= 5 * (40000 // 128 + 120)
     assert lib.lmi_invert_workspace_ints(10000, 4, 120) % 120 == 0
     import ctypes
-    offs = (ctypes.c_int64 * 12)()
+    offs = (ctypes.c_int64 * 13)()
     total = lib.lmi_workspace_layout(10000, 4, 120, 5, 768, offs)
-    assert total == offs[11] == lib.lmi_workspace_bytes(10000, 4, 120, 5) + 2 * 10000 * 768
+    assert total == offs[12] == lib.lmi_workspace_bytes(10000, 4, 120, 5) + 2 * 10000 * 768
+    assert offs[12] - offs[11] >= 4 * 10000 * 4 * 10 and offs[11] % 256 == 0  # LMI_WS_GATE: uint32[2*rmax, nq*B]
     assert all(offs[i] % 256 == 0 and offs[i] <= offs[i + 1] for i in range(11))
     assert offs[9] - offs[8] >= 4 * 40000 * 10 * 10  # part_sim: P * 2*rmax * 10 floats
 

@@ -190,7 +190,7 @@ def test_invert_matches_numpy():
             for r in range(nr):
                 for tq in range(tiles[b]):
                     exp_items.append((off[b] + r * ln, min(ln, s - r * ln), exp_off[b] + tq * 128,
-                                      min(128, m - tq * 128), 2 * r, b, tq, tiles[b]))
+                                      min(128, m - tq * 128), 2 * r | (2 * nr) << 16, b, tq, tiles[b]))
         assert np.array_equal(d_bl.cpu().numpy(), exp_bl)
         assert n_items == len(exp_items) <= max_items
         assert np.array_equal(items, np.array(exp_items, dtype=np.int32).reshape(-1, 8))
@@ -198,7 +198,7 @@ def test_invert_matches_numpy():
             assert len({it[1] for it in exp_items}) > 1
 
 
-@pytest.mark.parametrize("impl", [1, 0, 2], ids=["simt", "tcgen05", "tcgen05_pair"])
+@pytest.mark.parametrize("impl", [1, 0, 2, 3, 4], ids=["simt", "tcgen05", "tcgen05_pair", "tcgen05_n128", "tcgen05_n128_split"])
 @pytest.mark.parametrize("name", case_names())
 def test_search_matches_reference_golden(name, impl):
     c = GoldenCase(name)
@@ -229,7 +229,7 @@ def _synthetic(n, nq, C, seed_centres=300, steps=80):
     return X.numpy(), Q.numpy(), syn.layers_to_numpy(layers), pred.numpy()
 
 
-@pytest.mark.parametrize("impl", [1, 0, 2], ids=["simt", "tcgen05", "tcgen05_pair"])
+@pytest.mark.parametrize("impl", [1, 0, 2, 3, 4], ids=["simt", "tcgen05", "tcgen05_pair", "tcgen05_n128", "tcgen05_n128_split"])
 def test_search_matches_oracle_medium(impl):
     """Ragged real-sized buckets, several ranges per bucket, partial query tiles."""
     n, nq, C, B = 60_000, 1500, 24, 4
@@ -286,7 +286,7 @@ def test_cluster_pair_scan_equals_single_cta_scan(d, monkeypatch):
     qd = torch.from_numpy(Q).cuda()
     for B, k in [(1, 10), (2, 10), (3, 7), (C, 10)]:
         out = {}
-        for impl in (0, 2):
+        for impl in (0, 2, 3, 4):
             li = _index(layers, C, scan_impl=impl)
             li.attach_layout(layout)
             for rep in range(2):
@@ -294,6 +294,10 @@ def test_cluster_pair_scan_equals_single_cta_scan(d, monkeypatch):
             out[impl] = (dd.clone(), ii.clone(), int(li.last_plan["n_items"][0]))
         assert out[0][2] == out[2][2] and out[0][2] > 8
         assert torch.equal(out[0][0], out[2][0]) and torch.equal(out[0][1], out[2][1]), (d, B, k)
+        # impl 3: 128-row score tiles, one accumulator -- same work items, same answer
+        assert torch.equal(out[0][0], out[3][0]) and torch.equal(out[0][1], out[3][1]), (d, B, k, "n128")
+        # impl 4: the same tiles double buffered, the queries' k-blocks >= 8 in shared memory (d = 768 only uses them)
+        assert torch.equal(out[0][0], out[4][0]) and torch.equal(out[0][1], out[4][1]), (d, B, k, "n128 split")
 
 
 def test_f32_queries_and_float_inputs():

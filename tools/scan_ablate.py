@@ -1,10 +1,19 @@
 #!/usr/bin/env python
-"""Scan-kernel ablations on the headline workload (profiling aid, not a benchmark):
-times lmi_scan_topk with parts of the kernel switched off via LMI_SCAN_ABLATE
-(1 = no TMA loads, 2 = no candidate processing) and for several range lengths."""
-import argparse, os, sys, types
+"""Scan-kernel ablations on the headline workload (profiling aid, not a benchmark; results are WRONG
+when an ablation is set).  Needs the profile library (tools/build_profile_lib.sh); every configuration
+runs `--steps` back-to-back searches (sustained, i.e. under the board's power cap) with the SM clock and
+board power sampled, so the table gives the ENERGY per step of the kernel with parts switched off:
+
+  LMI_SCAN_ABLATE bits: 1 no TMA loads, 2 no candidate processing, 8 MMA-warp wait cycles, 16 stages
+  pre-filled with pseudo-random fp16 (MMAs without loads then multiply real data), 32 loads confined to a
+  50 MB window (L2 -> SM traffic as usual, nothing from HBM)
+
+    LMI_B200_PROFILE_LIBRARY=tools/liblmi_b200_profile.so python tools/scan_ablate.py --ablate 0,2,17,32,34
+"""
+import argparse, json, os, sys, time, types
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("LMI_B200_PROFILE_LIBRARY", os.path.join(ROOT, "tools", "liblmi_b200_profile.so"))
 import numpy as np
 import torch
 import bench
@@ -13,29 +22,45 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--n", type=int, default=10_000_000)
 ap.add_argument("--nq", type=int, default=10_000)
 ap.add_argument("--probe", type=int, default=4)
-ap.add_argument("--ranges", default="16384")
-ap.add_argument("--ablate", default="0,1,2,3")
+ap.add_argument("--ablate", default="0,2,17,32,34,0")
+ap.add_argument("--impls", default="0")
+ap.add_argument("--steps", type=int, default=150)
+ap.add_argument("--out", default="")
 a = ap.parse_args()
+assert os.path.isfile(os.environ["LMI_B200_PROFILE_LIBRARY"]), "build tools/liblmi_b200_profile.so first"
 args = types.SimpleNamespace(n=a.n, nq=a.nq, buckets=120, centres=2000, noise=0.25, latent=24, train_steps=300)
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
 from learnedmetricindex_b200 import DeviceBucketLayout, LearnedIndex
 w = bench.build_workload(args, dev, 0, 1)
-li = LearnedIndex(w["layers"], {}, [(i,) for i in range(120)])
-li.attach_layout(DeviceBucketLayout(w["vectors"], torch.from_numpy(w["bucket_off"]), w["ids"]))
+layout = DeviceBucketLayout(w["vectors"], torch.from_numpy(w["bucket_off"]), w["ids"])
 Q = w["Q"]
-for R in [int(x) for x in a.ranges.split(",")]:
-    os.environ["LMI_RANGE_ROWS"] = str(R)
+rows = []
+for impl in [int(x) for x in a.impls.split(",")]:
+    li = LearnedIndex(w["layers"], {}, [(i,) for i in range(120)], scan_impl=impl)
+    li.attach_layout(layout)
     for ab in [int(x) for x in a.ablate.split(",")]:
         os.environ["LMI_SCAN_ABLATE"] = str(ab)
-        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(20)]
         for _ in range(5):
             li.search_device(Q, Q, [120], a.probe, 10)
         torch.cuda.synchronize()
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(a.steps)]
+        smp = bench.ClockSampler(0, period_s=0.005)
+        smp.start()
+        t_a = time.time()
         for e in evs:
             li.search_device(Q, Q, [120], a.probe, 10, events=e)
         torch.cuda.synchronize()
-        scan = np.mean([e[2].elapsed_time(e[3]) for e in evs])
+        t_b = time.time()
+        smp.stop()
+        scan = np.array([e[2].elapsed_time(e[3]) for e in evs])
+        tail = scan[len(scan) // 3:]  # the power cap has settled by then
+        sel = [s for s in smp.samples if t_a + (t_b - t_a) / 3 <= s[0] <= t_b]
+        mhz = float(np.median([s[1] for s in sel])) if sel else None
+        watts = float(np.mean([s[3] for s in sel])) if sel else None
+        row = dict(impl=impl, ablate=ab, scan_ms_settled=float(tail.mean()), scan_ms_first5=float(scan[:5].mean()),
+                   sm_mhz=mhz, watts=watts, joule_per_scan=(watts * float(tail.mean()) / 1e3 if watts else None),
+                   mcycles=(mhz * float(tail.mean()) / 1e3 if mhz else None))
         if ab & 8:
             import ctypes
             from learnedmetricindex_b200 import _native
@@ -44,13 +69,11 @@ for R in [int(x) for x in a.ranges.split(",")]:
             _native.lib().lmi_debug_scan_profile(buf)
             pr = np.array(buf[:]).reshape(148, 8)
             names = ["total", "sched", "q_ready", "acc_empty", "full", "issue", "stages"]
-            print("   MMA-warp cycles (mean over CTAs):", {n: int(pr[:, i].mean()) for i, n in enumerate(names)},
-                  "total min/max", pr[:, 0].min(), pr[:, 0].max(), "stages min/max", pr[:, 6].min(), pr[:, 6].max())
-        import time
-        smp = bench.ClockSampler(0, period_s=0.005); smp.start(); t_a = time.time()
-        for _ in range(150):
-            li.search_device(Q, Q, [120], a.probe, 10)
-        torch.cuda.synchronize(); t_b = time.time(); smp.stop()
-        print("   clocks over %.2f s of back-to-back steps:" % (t_b - t_a), smp.summary([(t_a + 0.3, t_b)]))
-        print(f"range_rows={R} ablate={ab}: scan {scan:.3f} ms  n_items={int(li.last_plan['n_items'][0])}", flush=True)
+            row["mma_warp_cycles"] = {n: int(pr[:, i].mean()) for i, n in enumerate(names)}
+        rows.append(row)
+        print(json.dumps(row), flush=True)
 os.environ["LMI_SCAN_ABLATE"] = "0"
+if a.out:
+    with open(a.out, "w") as f:
+        for r in rows:
+            f.write(json.dumps(r) + "\n")

@@ -39,7 +39,7 @@ from learnedmetricindex_b200 import DeviceBucketLayout, LearnedIndex
 w = bench.build_workload(args, dev, 0, 1)
 layout = DeviceBucketLayout(w["vectors"], torch.from_numpy(w["bucket_off"]), w["ids"])
 Q = w["Q"]
-KNOBS = ("LMI_RANGE_ROWS", "LMI_TAIL_ROWS", "LMI_TAIL_PERMILLE", "LMI_SCAN_FLAGS", "LMI_SCAN_IMPL")
+KNOBS = ("LMI_RANGE_ROWS", "LMI_TAIL_ROWS", "LMI_TAIL_PERMILLE", "LMI_SCAN_FLAGS", "LMI_SCAN_IMPL", "LMI_SCAN_SHARE_GATE")
 # every configuration gets its own index object (the knobs are read when it plans its first search); the timed
 # bursts are INTERLEAVED round-robin, so the board's power/thermal state is the same for all of them
 cfgs = []
