@@ -90,6 +90,24 @@ def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_b
     return dict(range_len=main, tail_range_len=tail, tail_permille=permille, rmax=rmax)
 
 
+def results_to_host(owner, dists_d: torch.Tensor, nns_d: torch.Tensor):
+    """Device results -> fresh host arrays ``(dists f64, nns u32)`` (LearnedIndex.py:161): both D2H copies go into
+    pinned staging buffers kept per result shape on ``owner`` and are enqueued back to back, one synchronisation."""
+    cache = owner.__dict__.setdefault("_host_out", {})
+    key = (tuple(dists_d.shape), tuple(nns_d.shape))
+    buf = cache.get(key)
+    if buf is None:
+        if len(cache) >= 8:
+            cache.pop(next(iter(cache)))
+        buf = (torch.empty(dists_d.shape, dtype=torch.float64).pin_memory(),
+               torch.empty(nns_d.shape, dtype=torch.int32).pin_memory())
+        cache[key] = buf
+    buf[0].copy_(dists_d, non_blocking=True)
+    buf[1].copy_(nns_d, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return buf[0].numpy().copy(), buf[1].numpy().view(np.uint32).copy()
+
+
 class _BatchWorkspace:
     """Every transient array of one batch shape, in ONE allocation carved by ``lmi_workspace_layout``
     (SURVEY.md section 8b): a search allocates nothing but its two small result tensors."""
@@ -471,8 +489,7 @@ class LearnedIndex:
             qs = qn if queries_search is queries_navigation else to_device_matrix(queries_search, self.device)
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
             dists_d, nns_d = self.search_device(qn, qs, n_categories, n_buckets, k, events=ev)
-        dists = dists_d.cpu().numpy()
-        nns = nns_d.cpu().numpy().view(np.uint32)
+        dists, nns = results_to_host(self, dists_d, nns_d)
         stage = [ev[j].elapsed_time(ev[j + 1]) / 1e3 for j in range(4)]
         self._surface_query_rounding()
 

@@ -463,8 +463,9 @@ class ShardedLearnedIndex:
             d, i, ev = self.search_graphed(queries_navigation,
                                            queries_navigation if queries_search is queries_navigation else queries_search,
                                            list(n_categories), n_buckets, k)
-            dists = d.cpu().numpy()
-            nns = i.cpu().numpy().view(np.uint32)
+            from .LearnedIndex import results_to_host
+
+            dists, nns = results_to_host(self, d, i)
             stage = [ev[j].elapsed_time(ev[j + 1]) / 1e3 for j in range(4)]
             times.update(inference=stage[0], search_within_buckets=stage[1] + stage[2] + stage[3],
                          seq_search=stage[2], sort=stage[3])
