@@ -300,6 +300,41 @@ def test_cluster_pair_scan_equals_single_cta_scan(d, monkeypatch):
         assert torch.equal(out[0][0], out[4][0]) and torch.equal(out[0][1], out[4][1]), (d, B, k, "n128 split")
 
 
+def test_shared_gate_changes_the_partial_lists_only(monkeypatch):
+    """lmi_scan_topk's `gate` (the ranges of a bucket share a lower bound of the bucket's 10th best through global
+    memory): with and without it the merged result is bit-identical -- buckets of one list pair, of 2-4 lists
+    ((j, m) = (5, 2)) and of >= 5 lists ((2, 5)), exact distance ties included (every vector stored twice)."""
+    monkeypatch.setenv("LMI_RANGE_ROWS", "2048")
+    from learnedmetricindex_b200 import DeviceBucketLayout
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(11)
+    C, nq, d = 6, 900, 128
+    sizes = np.array([30000, 1500, 9000, 40, 4000, 2500])
+    base = rs.standard_normal((int(sizes.sum()) // 2, d)).astype(np.float32)
+    base = (base / np.linalg.norm(base, axis=1, keepdims=True)).astype(np.float16)
+    X = np.concatenate([base, base])  # duplicates: ties between rows of different ranges and buckets
+    pred = rs.permutation(np.repeat(np.arange(C), sizes)).astype(np.int64)
+    Q = rs.standard_normal((nq, d)).astype(np.float32)
+    Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+    layers = seeded_layers(5, "MLP", d, C, scale=2.0)
+    layout = DeviceBucketLayout.from_host(X, pred, C)
+    qd = torch.from_numpy(Q).cuda()
+    for impl in (0, 4):
+        for B, k in [(1, 10), (3, 10), (C, 7)]:
+            out = []
+            for share in ("1", "0"):
+                monkeypatch.setenv("LMI_SCAN_SHARE_GATE", share)
+                li = _index(layers, C, scan_impl=impl)
+                assert li.share_gate == (share == "1")
+                li.attach_layout(layout)
+                for rep in range(2):
+                    dd, ii = li.search_device(qd, qd, [C], B, k)
+                out.append((dd.clone(), ii.clone()))
+            assert li.last_plan["rmax"] >= 8  # the largest bucket has >= 16 lists
+            assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1]), (impl, B, k)
+
+
 def test_f32_queries_and_float_inputs():
     """f32 host inputs (the reference's documented dtype) take the cast path."""
     n, nq, C, B = 8000, 300, 8, 2
