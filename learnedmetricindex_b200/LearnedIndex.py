@@ -35,6 +35,7 @@ PER_BUCKET_K = 10  # `k` is not forwarded to _search_single_bucket (LearnedIndex
 MAX_RANGES = 32  # row ranges a bucket is cut into at most (lmi_merge_topk: <= 256 lists, <= 32 in its fast path)
 LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item writes per query
 SCAN_ROWS_PER_TILE = 64
+SCAN_MAX_D = 768  # widest search representation the tcgen05 scan kernels take (lmi_scan.cu: SCAN_MAX_D)
 DEFAULT_RANGE_ROWS = 24576  # upper bound on the rows of a scan work item (see plan_scan; sustained 10M sweep: 8192 +5 %, 16384 0, 24576 -1.9 %, 32768 -1.0 %)
 DEFAULT_SCAN_IMPL = 0
 GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index (least recently used goes first)
@@ -361,9 +362,19 @@ class LearnedIndex:
                                    ws.max_items, P[WS_INVERT_SCRATCH], st), "lmi_invert")
         mark(2)
         if layout.n > 0:
+            impl = self.scan_impl
+            if layout.d > SCAN_MAX_D and (impl & 0xff) != 1:
+                # the tcgen05 kernels keep a work item's queries in tensor memory (<= 768 dimensions); wider data
+                # still searches correctly, on the CUDA-core kernel -- far from the tensor roofline, so say so once
+                if not getattr(self, "_warned_wide", False):
+                    warnings.warn(f"search dimensionality {layout.d_data} > {SCAN_MAX_D}: the scan runs on the "
+                                  f"CUDA-core kernel (lmi_scan_topk impl 1), not on the tensor cores", UserWarning,
+                                  stacklevel=3)
+                    self._warned_wide = True
+                impl = 1
             _native.check(L.lmi_scan_topk(layout.vectors.data_ptr(), layout.n, layout.d, q16.data_ptr(), nq, B,
                                           P[WS_PAIR_LIST], P[WS_ITEMS], P[WS_N_ITEMS], ws.max_items, ws.lmax,
-                                          P[WS_PART_SIM], P[WS_PART_ROW], self.scan_impl | (self.scan_flags << 8),
+                                          P[WS_PART_SIM], P[WS_PART_ROW], impl | (self.scan_flags << 8),
                                           P[WS_GATE] if self.share_gate else None, st),
                           "lmi_scan_topk")
         mark(3)

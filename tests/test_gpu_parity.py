@@ -500,6 +500,29 @@ def test_dimensions_that_are_not_multiples_of_64(d):
     assert_search_parity(dd[same], ii[same], exp_d[same], exp_i[same], what=f"d={d}")
 
 
+def test_dimensionality_beyond_768_still_searches_correctly():
+    """d > 768 does not fit the tcgen05 kernels' tensor-memory budget: the search warns and takes the CUDA-core
+    scan kernel -- same work items, same answer as the oracle (the reference has no dimensionality limit)."""
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(1024)
+    d, n, nq, C, B = 1024, 3000, 150, 5, 2
+    X = rs.standard_normal((n, d)).astype(np.float32)
+    X = (X / np.linalg.norm(X, axis=1, keepdims=True)).astype(np.float16)
+    Q = rs.standard_normal((nq, d)).astype(np.float32)
+    Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+    layers = seeded_layers(77, "MLP-6", d, C, scale=4.0)
+    pred = orc.predict(layers, orc.to_f32_tensor(X)).astype(np.int64).reshape(-1, 1)
+    li = _index(layers, C)
+    with pytest.warns(UserWarning, match="CUDA-core kernel"):
+        dd, ii, _ = li.search(None, Q, X, Q, pred, [C], n_buckets=B, k=10)
+    exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=10)
+    probs, _ = orc.predict_proba(layers, orc.to_f32_tensor(Q))
+    same = _order_rows_equal(li.last_bucket_order.cpu().numpy(), exp_order[:, :, 0], probs)
+    assert same.mean() > 0.99
+    assert_search_parity(dd[same], ii[same], exp_d[same], exp_i[same], what="d=1024")
+
+
 def test_grouped_navigation_inference_equals_per_model_loop():
     """lmi_linear_tc_grouped (all models of a level in one launch, logits written straight into the
     node table) against the per-model launches: same split-precision arithmetic, so the
