@@ -20,6 +20,16 @@
 //     score matrix never leaves the SM.
 // Roles: warps 0-7 epilogue (+ query gather), warp 8 TMA producer + item scheduler,
 // warps 9-10 MMA issuers.
+//
+// Kernels in this file (lmi_scan_topk's `impl`; all write bit-identical merged results):
+//   scan_topk_tc_kernel<64, false>   impl 0, the product path described above, plus the gate the ranges of a
+//                                    bucket share through global memory (see the epilogue);
+//   scan_topk_tc_kernel<128, false>  impl 3: N = 128 score tiles, ONE accumulator (TMEM: 384 query columns + 128);
+//   scan_topk_tc_kernel<128, true>   impl 4: N = 128 tiles, TWO accumulators -- the queries' k-blocks 8..11 live in
+//                                    shared memory and enter their MMAs through a descriptor;
+//   scan_topk_pair_kernel            impl 2: clusters of two CTAs, bucket rows delivered by TMA multicast;
+//   scan_topk_simt_kernel            impl 1: CUDA-core verification kernel (any d; the path for d > 768).
+// Measured against each other in profiles/r02_scan_lab.md; DESIGN.md section 3.3 says why impl 0 stays the default.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>

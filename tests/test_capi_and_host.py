@@ -54,6 +54,9 @@ def test_sass_is_blackwell_native():
     assert "sm_100a" in sass
     for needle in ("UTCHMMA", "UTMALDG", "LDTM", "STTM"):
         assert needle in sass, needle
+    # the cluster-of-2 scan (lmi_scan_topk impl 2): multicast TMA loads and the multicast tcgen05.commit
+    for needle in ("UTMALDG.2D.MULTICAST", "UTCBAR.MULTICAST"):
+        assert needle in sass, needle
     assert "HMMA." not in sass.replace("UTCHMMA", "")
 
 
