@@ -14,8 +14,6 @@ from ctypes import c_char_p, c_int, c_int64, c_void_p
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "liblmi_b200.so")
-# tools/ only: a library built with -DLMI_PROFILE (tools/build_profile_lib.sh) is loaded from here instead
-_PROFILE_LIB = os.environ.get("LMI_B200_PROFILE_LIBRARY")
 SOURCES = ["lmi_mlp.cu", "lmi_mlp_tc.cu", "lmi_invert.cu", "lmi_scan.cu", "lmi_merge.cu", "lmi_layout.cu", "lmi_navigate.cu", "lmi_nav_fused.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -107,7 +105,7 @@ def lib() -> ctypes.CDLL:
         raise RuntimeError(
             f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(learnedmetricindex_b200 has no CPU fallback)")
-    handle = ctypes.CDLL(_PROFILE_LIB if _PROFILE_LIB and os.path.isfile(_PROFILE_LIB) else LIB_PATH)
+    handle = ctypes.CDLL(LIB_PATH)
     for name, (res, args) in _SIGNATURES.items():
         fn = getattr(handle, name)
         fn.restype = res

@@ -8,15 +8,20 @@ board power sampled, so the table gives the ENERGY per step of the kernel with p
   pre-filled with pseudo-random fp16 (MMAs without loads then multiply real data), 32 loads confined to a
   50 MB window (L2 -> SM traffic as usual, nothing from HBM)
 
-    LMI_B200_PROFILE_LIBRARY=tools/liblmi_b200_profile.so python tools/scan_ablate.py --ablate 0,2,17,32,34
+    tools/build_profile_lib.sh && python tools/scan_ablate.py --ablate 0,2,17,32,34
 """
 import argparse, json, os, sys, time, types
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-os.environ.setdefault("LMI_B200_PROFILE_LIBRARY", os.path.join(ROOT, "tools", "liblmi_b200_profile.so"))
 import numpy as np
 import torch
 import bench
+from learnedmetricindex_b200 import _native
+
+# the product package knows nothing about the profile build: point its loader at it before the first lib() call
+PROFILE_LIB = os.path.join(ROOT, "tools", "liblmi_b200_profile.so")
+assert os.path.isfile(PROFILE_LIB), "build tools/liblmi_b200_profile.so first (tools/build_profile_lib.sh)"
+_native.LIB_PATH = PROFILE_LIB
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--n", type=int, default=10_000_000)
@@ -27,7 +32,6 @@ ap.add_argument("--impls", default="0")
 ap.add_argument("--steps", type=int, default=150)
 ap.add_argument("--out", default="")
 a = ap.parse_args()
-assert os.path.isfile(os.environ["LMI_B200_PROFILE_LIBRARY"]), "build tools/liblmi_b200_profile.so first"
 args = types.SimpleNamespace(n=a.n, nq=a.nq, buckets=120, centres=2000, noise=0.25, latent=24, train_steps=300)
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
