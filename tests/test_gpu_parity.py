@@ -129,7 +129,8 @@ def test_invert_matches_numpy():
     L = _native.lib()
     rs = np.random.RandomState(5)
     cases = [(1, 1, 7, 64, 0, 0), (37, 3, 11, 128, 0, 0), (5000, 4, 120, 1024, 0, 0), (20000, 16, 50, 4096, 0, 0),
-             (5000, 4, 120, 1024, 256, 300), (3000, 7, 1500, 2048, 512, 150)]  # last two: two-level cut, C > 1024
+             (5000, 4, 120, 1024, 256, 300), (3000, 7, 1500, 2048, 512, 150),  # two-level cut, C > 1024
+             (2000, 5, 1000, 1024, 256, 200), (40000, 4, 120, 1024, 0, 0)]
     for nq, B, C, rng_len, tail_len, tail_pm in cases:
         order = np.stack([rs.permutation(C)[:B] for _ in range(nq)]).astype(np.int32)
         order[rs.rand(nq, B) < 0.02] = -1  # ignored entries
