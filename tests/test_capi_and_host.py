@@ -98,10 +98,10 @@ def test_plan_scan(nq, B, C, n, maxb):
     from learnedmetricindex_b200 import plan_scan
     from learnedmetricindex_b200.LearnedIndex import MAX_RANGES
 
-    for nonempty in (None, max(1, C // 8)):
-        p = plan_scan(nq, B, C, n, maxb, n_nonempty=nonempty)
+    for nonempty, tile in ((None, 64), (max(1, C // 8), 64), (None, 128)):
+        p = plan_scan(nq, B, C, n, maxb, n_nonempty=nonempty, rows_per_tile=tile)  # 128: lmi_scan_topk impl 3 / 4
         length, tail, rmax = p["range_len"], p["tail_range_len"], p["rmax"]
-        assert length % 64 == 0 and length >= 64
+        assert length % tile == 0 and length >= tile
         assert 1 <= rmax <= MAX_RANGES
         shortest = tail or length
         assert tail % 64 == 0 and tail < length and 0 <= p["tail_permille"] <= 400

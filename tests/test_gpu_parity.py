@@ -568,7 +568,8 @@ def test_grouped_navigation_inference_equals_per_model_loop():
         assert torch.equal(o1, o2)
 
 
-def test_property_ragged_buckets_match_oracle():
+@pytest.mark.parametrize("impl", [0, 4], ids=["tcgen05", "tcgen05_n128_split"])
+def test_property_ragged_buckets_match_oracle(impl):
     """Hypothesis over ragged bucket sizes (incl. s_b < 10 and empty buckets), query counts that
     leave partial tiles, B = 1 .. C, k <= 10 and odd dimensionalities."""
     from hypothesis import given, settings, strategies as st, HealthCheck
@@ -592,14 +593,14 @@ def test_property_ragged_buckets_match_oracle():
         Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
         layers = seeded_layers(seed + 5, "MLP-8", d, C, scale=4.0)
         ids = rs.permutation(np.arange(7, 7 + n))
-        li = _index(layers, C)
+        li = _index(layers, C, scan_impl=impl)
         li.attach_layout(DeviceBucketLayout.from_host(X, pred[:, 0], C, ids=ids))
         dd, ii, _ = li.search(None, Q, None, Q, None, [C], n_buckets=B, k=k)
         exp_d, exp_i, _, exp_order = orc.search(orc.OracleIndex(layers), Q, X, Q, pred, [C], n_buckets=B, k=k, ids=ids)
         probs, _ = orc.predict_proba(layers, orc.to_f32_tensor(Q))
         same = _order_rows_equal(li.last_bucket_order.cpu().numpy(), exp_order[:, :, 0], probs)
         assert_search_parity(dd[same], ii[same], exp_d[same], exp_i[same],
-                             what=f"seed={seed} C={C} nq={nq} d={d} B={B} k={k} sizes={sizes.tolist()}")
+                             what=f"impl={impl} seed={seed} C={C} nq={nq} d={d} B={B} k={k} sizes={sizes.tolist()}")
 
     run()
 
