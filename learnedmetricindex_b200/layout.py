@@ -160,16 +160,20 @@ class DeviceBucketLayout:
         return DeviceBucketLayout(vec, torch.from_numpy(new_off), self.ids[sel].contiguous(), self.bucket_paths,
                                   d_data=self.d_data, inexact_values=self.inexact_values)
 
-    def restrict_to_slice(self, rank: int, world: int) -> "DeviceBucketLayout":
+    def restrict_to_slice(self, rank: int, world: int, shares=None) -> "DeviceBucketLayout":
         """Shard: keep rows ``[s_b*rank//world, s_b*(rank+1)//world)`` of EVERY bucket -- every rank
         then scans the same buckets for the same probes with 1/world of the rows (perfectly balanced).
+        ``shares[r]``: relative scan throughput of rank r; its slice is then that fraction of every bucket.
         Valid for ``k <= 10``: an object ranked beyond 10 inside its bucket cannot reach the overall
         top 10, so merging the ranks' lists gives the unsharded result (filler ids of undersized
         buckets excepted)."""
+        from .sharded import slice_bounds
+
         off = self.bucket_off_host
         sizes = np.diff(off)
-        lo = off[:-1] + sizes * rank // world
-        hi = off[:-1] + sizes * (rank + 1) // world
+        lo_all, hi_all = slice_bounds(sizes, world, shares)
+        lo = off[:-1] + lo_all[rank]
+        hi = off[:-1] + hi_all[rank]
         new_off = np.zeros(self.n_buckets + 1, dtype=np.int64)
         new_off[1:] = np.cumsum(hi - lo)
         rows = [torch.arange(a, b, device=self.device) for a, b in zip(lo.tolist(), hi.tolist()) if b > a]

@@ -25,23 +25,46 @@ import torch
 import torch.distributed as dist
 
 
-def partition_buckets(sizes: Sequence[int], world: int, weights: Optional[Sequence[float]] = None) -> List[List[int]]:
+def partition_buckets(sizes: Sequence[int], world: int, weights: Optional[Sequence[float]] = None,
+                      speeds: Optional[Sequence[float]] = None) -> List[List[int]]:
     """Longest-processing-time greedy assignment of whole buckets to ``world`` ranks.
 
     ``sizes[b]`` = rows of bucket b; ``weights[b]`` (optional) = expected probes of bucket b,
     so the balanced quantity is scan work ``s_b * w_b`` (HBM bytes when all weights are 1).
+    ``speeds[r]`` (optional) = relative scan throughput of rank r -- the GPUs of one box differ by several
+    percent under their power caps -- a bucket then goes to the rank that would FINISH it earliest.
     Deterministic: ties go to the lower bucket id / lower rank, so every rank derives the
     same map without communicating."""
     sizes = np.asarray(sizes, dtype=np.float64)
     cost = sizes if weights is None else sizes * np.asarray(weights, dtype=np.float64)
+    speed = np.ones(world) if speeds is None else np.asarray(speeds, dtype=np.float64)
+    assert speed.shape == (world,) and (speed > 0).all()
     order = sorted(range(len(sizes)), key=lambda b: (-cost[b], b))
     load = [0.0] * world
     mine: List[List[int]] = [[] for _ in range(world)]
     for b in order:
-        r = min(range(world), key=lambda w: (load[w], w))
+        r = min(range(world), key=lambda w: ((load[w] + float(cost[b])) / speed[w] if speeds is not None else load[w], w))
         mine[r].append(b)
         load[r] += float(cost[b])
     return [sorted(m) for m in mine]
+
+
+def slice_bounds(sizes: Sequence[int], world: int, shares: Optional[Sequence[float]] = None):
+    """Row slice ``[lo_b, hi_b)`` of every bucket for each rank: ``(lo[world, C], hi[world, C])``.  Equal slices by
+    default; ``shares[r]`` (relative scan throughput of rank r) makes rank r's slice that fraction of every bucket.
+    The slices are contiguous and in rank order, which the cross-GPU merge's tie order relies on."""
+    sizes = np.asarray(sizes, dtype=np.int64)
+    if shares is None:
+        cuts = [sizes * r // world for r in range(world + 1)]
+    else:
+        sh = np.asarray(shares, dtype=np.float64)
+        assert sh.shape == (world,) and (sh > 0).all()
+        cum = np.concatenate(([0.0], np.cumsum(sh) / sh.sum()))
+        cuts = [np.floor(sizes * c + 1e-9).astype(np.int64) for c in cum]
+        cuts[-1] = sizes.copy()
+    lo = np.stack(cuts[:-1])
+    hi = np.stack(cuts[1:])
+    return lo, np.maximum(hi, lo)
 
 
 def owner_of_bucket(parts: List[List[int]], n_buckets: int) -> np.ndarray:

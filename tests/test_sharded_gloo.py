@@ -36,6 +36,27 @@ def test_partition_buckets_balances_and_is_deterministic():
     # more ranks than buckets: some ranks own nothing, nothing is lost
     parts = partition_buckets([5, 3], 4)
     assert sorted(b for p in parts for b in p) == [0, 1]
+    # ranks of different speed (GPUs of one box differ under their power caps): finish times are balanced
+    speeds = np.array([1.0, 0.9, 1.1, 1.0, 0.92, 1.05, 1.0, 0.95])
+    parts = partition_buckets(sizes, 8, speeds=speeds)
+    assert sorted(b for p in parts for b in p) == list(range(120))
+    t = np.array([sizes[p].sum() for p in parts]) / speeds
+    assert t.max() / t.mean() < 1.05
+    t_blind = np.array([sizes[p].sum() for p in partition_buckets(sizes, 8)]) / speeds
+    assert t.max() < t_blind.max()
+
+
+def test_slice_bounds_cover_every_bucket_in_rank_order():
+    from learnedmetricindex_b200.sharded import slice_bounds
+
+    sizes = np.array([0, 1, 7, 10, 83_333, 1_000_003])
+    for shares in (None, [1.0, 0.9, 1.1, 1.0], [3.0, 1.0, 1.0, 1.0]):
+        lo, hi = slice_bounds(sizes, 4, shares)
+        assert (lo[0] == 0).all() and (hi[-1] == sizes).all()
+        assert (lo[1:] == hi[:-1]).all() and (hi >= lo).all()  # contiguous, in rank order, nothing lost
+        if shares is not None:
+            frac = (hi - lo)[:, -1] / sizes[-1]
+            np.testing.assert_allclose(frac, np.array(shares) / np.sum(shares), atol=1e-5)
 
 
 def _numpy_merge(buf, out_d, out_i):
