@@ -37,11 +37,13 @@
  * Conventions
  *   - extern "C", plain pointers and sizes; no C++/torch types.
  *   - every pointer is a DEVICE pointer owned by the caller unless the name ends
- *     in _host; nothing is allocated or freed inside, nothing is retained.
+ *     in _host; nothing is allocated or freed inside, nothing is retained.  Scratch is passed in by the
+ *     caller too -- or, for callers that cannot allocate any, see lmi_invert_static.
  *   - `stream` is a cudaStream_t passed as void*; calls only enqueue work.
  *   - return value: 0 on success, a positive cudaError_t, or a negative LMI_E_*.
  *     lmi_error_string() renders either.  No exceptions cross the boundary.
- *   - thread-safety: stateless; concurrent calls on different streams are fine.
+ *   - thread-safety: stateless; concurrent calls on different streams are fine (one exception, documented at
+ *     its declaration: lmi_invert_static, whose scratch is one array per GPU shared by all of its calls).
  *   - there is no CPU fallback: every entry point launches sm_100a kernels.
  */
 #ifndef LMI_B200_H_
@@ -53,11 +55,12 @@
 extern "C" {
 #endif
 
-#define LMI_B200_ABI_VERSION 6
+#define LMI_B200_ABI_VERSION 7
 
 #define LMI_E_BADARG (-1)      /* null pointer / non-positive size / unsupported shape */
 #define LMI_E_UNSUPPORTED (-2) /* shape outside what the sm_100a kernels implement */
 #define LMI_E_DRIVER (-3)      /* CUDA driver entry point (tensor map encode) unavailable */
+#define LMI_E_SCRATCH_LIMIT (-4) /* lmi_invert_static: the batch needs more than the built-in scratch array */
 
 #define LMI_PER_BUCKET_K 10 /* `k` is not forwarded to _search_single_bucket (LearnedIndex.py:111-117,:334) */
 #define LMI_ITEM_WORDS 8    /* int32 words per scan work item, see lmi_invert */
@@ -231,6 +234,44 @@ int lmi_invert(const int32_t *bucket_order, int nq, int B, int C, const int64_t 
                int32_t *counts, int32_t *offsets, int32_t *bucket_lists,
                int32_t *pair_list, int32_t *slot_of_pair, int32_t *items, int32_t *n_items,
                int64_t max_items, int32_t *workspace, void *stream);
+
+/* lmi_invert for callers that have no device memory to give it as scratch.  (No counterpart in the reference:
+ * it is the same replacement of filter_path_idxs as lmi_invert; only where the scratch comes from differs.)
+ *
+ * Who needs it: code that runs where allocating device memory is off the table.  A plugin living inside a
+ * host application (a database operator, a serving backend) is typically handed fixed input/output buffers
+ * and a stream, and must not touch the allocator: the host has already claimed the GPU's memory for its own
+ * pool, so a cudaMalloc from the plugin either fails or breaks the footprint the host budgeted.  A
+ * latency-critical serving thread cannot take the device-wide synchronisation that cudaMalloc / cudaFree
+ * imply.  And a caller written in another language over FFI may simply have no device allocator to call.
+ * Such callers can still own the OUTPUT arrays below (they are the result, sized by the host), but the
+ * per-chunk histograms of lmi_invert are pure scratch -- so this variant keeps them in an array that is part
+ * of the library image itself: LMI_INVERT_STATIC_MAX_INTS int32 = 4 MiB on every GPU that loads the library,
+ * held until the process exits.  The call performs no cudaMalloc / cudaFree and calls nothing that allocates.
+ *
+ * Arguments and outputs: exactly lmi_invert's, minus `workspace`; the outputs are bit-identical to lmi_invert's.
+ *
+ * Limit: lmi_invert_workspace_ints(nq, B, C) <= LMI_INVERT_STATIC_MAX_INTS, checked before anything is
+ * launched; beyond it the call returns LMI_E_SCRATCH_LIMIT and writes nothing (use lmi_invert with your own
+ * scratch).  The headline batch (10 000 queries x 4 probes, 120 buckets) needs 18 720 ints; 100 000 queries x
+ * 120 probes over 120 buckets needs 491 520; the limit is first hit at 4096 chunks x more than 256 buckets.
+ *
+ * First call on each device: the library looks up where its array lives on the device that is current on the
+ * calling thread (cudaGetSymbolAddress, result cached per device, return code checked).  That look-up can
+ * make the runtime load the module, so make the first call on a device with that device current, on the
+ * stream's own device, and BEFORE you begin any stream capture; later calls only enqueue the three kernels.
+ *
+ * Sharing: there is ONE array per GPU and every call on that GPU uses it.  Nothing has to be cleared between
+ * calls (the first pass zeroes the cells it is about to count into, so the previous call's leftovers are never
+ * read), but two calls whose kernels can be in flight at the same time -- different streams, or different
+ * host threads on different streams -- overwrite each other's histograms and produce garbage.  Keep all
+ * calls for one GPU on one stream, or order them with events.  lmi_invert has no such restriction. */
+#define LMI_INVERT_STATIC_MAX_INTS (1 << 20)
+int lmi_invert_static(const int32_t *bucket_order, int nq, int B, int C, const int64_t *bucket_off,
+                      int range_len, int tail_range_len, int tail_permille,
+                      int32_t *counts, int32_t *offsets, int32_t *bucket_lists,
+                      int32_t *pair_list, int32_t *slot_of_pair, int32_t *items, int32_t *n_items,
+                      int64_t max_items, void *stream);
 
 /* ---- candidate scan + fused per-range top-10 ---------------------------------- */
 

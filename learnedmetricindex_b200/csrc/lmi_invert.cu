@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "../../include/lmi_b200.h"
 
 namespace lmi {
@@ -297,6 +299,75 @@ extern "C" int lmi_invert(const int32_t* bucket_order, int nq, int B, int C, con
                                                 counts, offsets, bucket_lists, items, n_items, max_items);
     lmi::invert_scatter_kernel<<<blocks, lmi::INV_WARPS_PER_BLOCK * 32, 0, st>>>(bucket_order, P, C, G, chunk,
                                                                                  bucket_off, workspace, offsets,
+                                                                                 pair_list, slot_of_pair);
+    return static_cast<int>(cudaGetLastError());
+}
+
+// ---- lmi_invert_static: the same three passes with the histogram scratch inside the library ----------------
+//
+// The scratch lives in the module image instead of in a caller allocation: LMI_INVERT_STATIC_MAX_INTS int32
+// (4 MiB) that every GPU which loads this library carries until the process exits.  `g_invert_scratch` below is
+// what HOST code sees of it -- a stand-in the runtime uses as a lookup key, NOT an address a kernel can
+// dereference -- so the host asks the runtime where the array sits on the CURRENT device
+// (cudaGetSymbolAddress) and hands that pointer to the kernels like any other workspace.
+namespace lmi {
+
+static __device__ __align__(256) int32_t g_invert_scratch[LMI_INVERT_STATIC_MAX_INTS];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::mutex g_static_mu;
+static int32_t* g_static_ptr[STATIC_MAX_DEVICES];  // per-device address of g_invert_scratch, filled on first use
+
+// Address of the scratch array on the device that is current on the calling thread.  The first call per
+// device resolves the symbol (this may load the module on that device, which is why it has to happen
+// outside stream capture); later calls read the cached pointer.
+static int static_scratch(int32_t** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES) return LMI_E_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_invert_scratch);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        if (!p) return LMI_E_DRIVER;
+        g_static_ptr[dev] = static_cast<int32_t*>(p);
+    }
+    *out = g_static_ptr[dev];
+    return 0;
+}
+
+}  // namespace lmi
+
+extern "C" int lmi_invert_static(const int32_t* bucket_order, int nq, int B, int C, const int64_t* bucket_off,
+                                 int range_len, int tail_range_len, int tail_permille, int32_t* counts,
+                                 int32_t* offsets, int32_t* bucket_lists, int32_t* pair_list, int32_t* slot_of_pair,
+                                 int32_t* items, int32_t* n_items, int64_t max_items, void* stream) {
+    if (!bucket_order || !bucket_off || !counts || !offsets || !bucket_lists || !pair_list || !slot_of_pair ||
+        !items || !n_items)
+        return LMI_E_BADARG;
+    if (nq <= 0 || B <= 0 || C <= 0 || range_len <= 0 || range_len % 64 != 0 || max_items <= 0) return LMI_E_BADARG;
+    if (tail_permille < 0 || tail_permille > 1000 || tail_range_len < 0 || tail_range_len % 64 != 0) return LMI_E_BADARG;
+    const int64_t P = (int64_t)nq * B;
+    if (P > 0x7fffffffLL) return LMI_E_UNSUPPORTED;
+    const int G = lmi::inv_num_chunks(P);
+    // the whole scratch need of this shape, checked BEFORE anything is launched: chunks x buckets histogram cells
+    if ((int64_t)G * C > (int64_t)LMI_INVERT_STATIC_MAX_INTS) return LMI_E_SCRATCH_LIMIT;
+    int32_t* scratch = nullptr;
+    const int rc = lmi::static_scratch(&scratch);
+    if (rc != 0) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t chunk = lmi::inv_chunk_len(P, G);
+    const int blocks = (G + lmi::INV_WARPS_PER_BLOCK - 1) / lmi::INV_WARPS_PER_BLOCK;
+    // nothing to clear by hand: pass 1 zeroes every histogram row it is about to count into, so what the
+    // previous call (of any shape) left in the array is never read
+    lmi::invert_hist_kernel<<<blocks, lmi::INV_WARPS_PER_BLOCK * 32, 0, st>>>(bucket_order, P, C, G, chunk, bucket_off,
+                                                                              scratch);
+    lmi::invert_scan_kernel<<<1, 1024, 0, st>>>(scratch, C, G, bucket_off, range_len, tail_range_len, tail_permille,
+                                                counts, offsets, bucket_lists, items, n_items, max_items);
+    lmi::invert_scatter_kernel<<<blocks, lmi::INV_WARPS_PER_BLOCK * 32, 0, st>>>(bucket_order, P, C, G, chunk,
+                                                                                 bucket_off, scratch, offsets,
                                                                                  pair_list, slot_of_pair);
     return static_cast<int>(cudaGetLastError());
 }

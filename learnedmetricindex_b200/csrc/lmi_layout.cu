@@ -101,6 +101,9 @@ extern "C" const char* lmi_error_string(int code) {
         case LMI_E_BADARG: return "lmi: bad argument";
         case LMI_E_UNSUPPORTED: return "lmi: shape not supported by the sm_100a kernels";
         case LMI_E_DRIVER: return "lmi: CUDA driver entry point unavailable / tensor map encode failed";
+        case LMI_E_SCRATCH_LIMIT:
+            return "lmi: batch needs more scratch than the library's built-in array holds "
+                   "(lmi_invert_static: lmi_invert_workspace_ints > LMI_INVERT_STATIC_MAX_INTS); use lmi_invert";
         default: break;
     }
     if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));

@@ -24,7 +24,7 @@ def test_library_builds_loads_and_exports_header_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/lmi_b200.h but not exported"
     assert set(declared) == set(_native.EXPORTED_SYMBOLS), "ctypes signatures out of sync with the header"
-    assert lib.lmi_version() == 6
+    assert lib.lmi_version() == 7
     assert lib.lmi_error_string(0) == b"success"
     assert b"bad argument" in lib.lmi_error_string(-1)
     # size helpers are pure host functions
