@@ -293,10 +293,13 @@ int lmi_invert_static(const int32_t *bucket_order, int nq, int B, int C, const i
  *             result is unchanged.  The call resets the array itself.
  * impl (low 8 bits; every value gives bit-identical lists):
  *   0 = tcgen05/TMA kernel, one CTA per work item, 64-row score tiles, two accumulators (product path)
- *   1 = plain CUDA-core verification kernel (tests only; any d)
+ *   1 = plain CUDA-core kernel, any d: the verification path of the tests, and what a search with d > 768 runs
+ *       on (correct, far from the roofline; learnedmetricindex_b200 warns when it takes it)
  *   2 = the impl-0 kernel over thread-block clusters of two CTAs: two query tiles of one (bucket, range)
  *       receive the bucket rows by ONE multicast TMA load (measured: not faster)
  *   3 = 128-row score tiles (N = 128 MMAs, half the A-operand reads per flop), one accumulator
+ *   4 = 128-row score tiles with the queries split between tensor memory (K-blocks 0-7) and shared memory
+ *       (K-blocks 8-11), which leaves room for two accumulators (measured: not faster than 0)
  * impl >> 8: tuning flags (bit 0: L2 eviction hints by sibling order); results do not depend on them.
  */
 int lmi_scan_topk(const void *X, int64_t n, int d, const void *Q, int nq, int B,

@@ -3,10 +3,12 @@
 
 Same constructor (:23-28), same ``search`` signature, return dtypes and id semantics
 (:41-51, :161): ``(dists f64[nq,k], nns u32[nq,k], measured_time)``.  The reference's
-``B x n_buckets_in_index`` Python double loop (:107 x :350) becomes four launches:
+``B x n_buckets_in_index`` Python double loop (:107 x :350) becomes four stages, six launches, replayed
+as ONE CUDA graph per search:
 
-    MLP + softmax + top-B        lmi_linear / lmi_softmax_topn     (model.py:226-241)
-    query-to-bucket inversion    lmi_invert                        (utils.py:61-65)
+    MLP + softmax + top-B        lmi_mlp_topn, one launch (tcgen05 tf32x3; per-layer lmi_linear_tc +
+                                 lmi_softmax_topn for shapes it does not take)  (model.py:226-241)
+    query-to-bucket inversion    lmi_invert, three launches        (utils.py:61-65)
     bucket scan + fused top-10   lmi_scan_topk (tcgen05 / TMA)     (LearnedIndex.py:350-365)
     merge across probes          lmi_merge_topk                    (LearnedIndex.py:125-146, :368-371)
 
@@ -425,21 +427,20 @@ class LearnedIndex:
 
         tn = as_tensor(qn)
         ts = tn if shared else as_tensor(qs)
-        # a contiguous DEVICE matrix is read in place (the graph is keyed on its address); anything else is
-        # copied into a static device buffer before every replay
-        in_place = lambda t: t.is_cuda and t.is_contiguous()
+        # the key holds nothing but shapes, dtypes and the budget: inputs -- host or device -- are always copied
+        # into the entry's static device buffers (a device-to-device copy of the batch costs microseconds next
+        # to the scan), so a caller that hands over a freshly allocated device tensor per call still replays
+        # the one captured graph instead of re-capturing on every new address
         key = (tuple(tn.shape), tn.dtype, tuple(ts.shape), ts.dtype, shared, tuple(n_categories), int(n_buckets),
-               int(k), id(self._layout), self.scan_impl, tn.data_ptr() if in_place(tn) else 0,
-               ts.data_ptr() if in_place(ts) else 0)
+               int(k), id(self._layout), self.scan_impl)
         entry = self._graphs.get(key)
         if entry is None:
             if len(self._graphs) >= GRAPH_CACHE:
                 self._graphs.popitem(last=False)  # least recently used
-            sn = tn if in_place(tn) else torch.empty(tn.shape, dtype=tn.dtype, device=self.device)
-            ss = sn if shared else (ts if in_place(ts) else torch.empty(ts.shape, dtype=ts.dtype, device=self.device))
-            if sn is not tn:
-                sn.copy_(tn, non_blocking=True)
-            if not shared and ss is not ts:
+            sn = torch.empty(tn.shape, dtype=tn.dtype, device=self.device)
+            ss = sn if shared else torch.empty(ts.shape, dtype=ts.dtype, device=self.device)
+            sn.copy_(tn, non_blocking=True)
+            if not shared:
                 ss.copy_(ts, non_blocking=True)
             # eager run first: fills every lazy cache (weight splits, workspaces, the tensor-map driver entry
             # point, the navigation tree) outside the capture
@@ -457,7 +458,7 @@ class LearnedIndex:
             self._graphs[key] = entry
         else:
             self._graphs.move_to_end(key)
-            if entry["qn"] is not tn:
+            if entry["qn"] is not tn:  # (a caller may pass the static buffer itself: nothing to copy then)
                 entry["qn"].copy_(tn, non_blocking=True)
             if not shared and entry["qs"] is not ts:
                 entry["qs"].copy_(ts, non_blocking=True)

@@ -353,7 +353,17 @@ nav_fused_kernel(const __grid_constant__ NfMaps maps, const __half* __restrict__
         // ticket: the last CTA of this query tile to arrive finishes the job (below, with every warp)
         __threadfence();
         nf_named_barrier(1, NF_EPI_THREADS);
-        if (threadIdx.x == 0) bars->ticket = atomicAdd(tile_counter + tile, 1);
+        if (threadIdx.x == 0) {
+            // release / acquire in the thread that owns the atomic: the barrier above made every epilogue
+            // thread's partials visible to this thread, the fence before the atomic publishes them (fences are
+            // cumulative) together with the ticket, and the fence after it orders the finishing CTA's reads of
+            // the OTHER CTAs' partials behind the ticket value that proved them written.  The __syncthreads
+            // below hands that ordering to the rest of the CTA.
+            __threadfence();
+            const int32_t t = atomicAdd(tile_counter + tile, 1);
+            __threadfence();
+            bars->ticket = t;
+        }
     }
 
     ptx::tc_fence_before();
@@ -407,7 +417,10 @@ nav_fused_kernel(const __grid_constant__ NfMaps maps, const __half* __restrict__
             logits_out[(size_t)(m0 + r) * C + c] = lall[(size_t)r * (NF_CP_MAX + 1) + c];
         }
     }
-    if (threadIdx.x == 0) tile_counter[tile] = 0;  // ready for the next launch
+    // ready for the next launch.  The counters reset themselves, which is only sound with ONE launch in flight per
+    // workspace: launches that share a workspace must be ordered on a stream (the host side keeps one workspace
+    // per batch size and issues every search of an index on the caller's current stream).
+    if (threadIdx.x == 0) tile_counter[tile] = 0;
     if (order && threadIdx.x < NF_BM && m0 + (int)threadIdx.x < nq) {
         // softmax (model.py:238) and the B most probable classes, ties to the lower class index -- the same
         // formulas as softmax_topn_kernel; one thread per query row

@@ -154,6 +154,13 @@ __device__ __forceinline__ uint32_t gate_encode(float f) {
 __device__ __forceinline__ float gate_decode(uint32_t u) {
     return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
+// A value strictly below `bound` to gate with (`score > gate_below(bound)`), so that a score EQUAL to a bound that
+// another list published still reaches the (similarity, row)-keyed merge, where the lower row wins the tie.  Two
+// ulps relative for ordinary values; an absolute step of FLT_MIN where the relative one vanishes -- a bound of
+// exactly 0.0 (all-zero queries or rows, padding) or a denormal-sized one -- and -inf stays -inf.
+__device__ __forceinline__ float gate_below(float bound) {
+    return bound - fmaxf(fabsf(bound) * 2.4e-7f, 1.17549435e-38f);
+}
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
     uint32_t v;
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -576,10 +583,10 @@ scan_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __re
                 // the other half's 10th best, nudged down so that an exact tie with it still
                 // reaches the (similarity, row)-keyed merge
                 const float og = *gate_other;
-                tau = fmaxf(tau, og - fabsf(og) * 2.4e-7f);
+                tau = fmaxf(tau, gate_below(og));
                 if (gq != 0u) {  // same nudge: an exact tie with the bound still reaches the merge
                     const float gg = gate_decode(gq);
-                    tau = fmaxf(tau, gg - fabsf(gg) * 2.4e-7f);
+                    tau = fmaxf(tau, gate_below(gg));
                 }
                 ptx::tmem_ld_wait();
                 ptx::tc_fence_before();
@@ -917,7 +924,7 @@ scan_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __half* __
                 uint32_t v[32];
                 ptx::tmem_ld32(tmem + lane_field + TMEM_ACC_COL + buf * SCAN_N + h * 32, v);
                 const float og = *gate_other;
-                tau = fmaxf(tau, og - fabsf(og) * 2.4e-7f);
+                tau = fmaxf(tau, gate_below(og));
                 ptx::tmem_ld_wait();
                 ptx::tc_fence_before();
                 __syncwarp();

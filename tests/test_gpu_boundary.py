@@ -286,3 +286,63 @@ def test_rank_merge_orders_equal_distances_by_probe_rank_then_gpu_rank():
             o = np.lexsort((fpos, fr, fp, fd))[:k]
             np.testing.assert_array_equal(got_d[q], fd[o])
             np.testing.assert_array_equal(got_i[q], ids[:, q].reshape(-1)[o])
+
+
+def test_peer_merge_and_peer_gather_kernels_on_one_gpu():
+    """lmi_merge_ranks_peer and lmi_gather_peer take a device array of per-rank base pointers, so they can be
+    proven on ONE GPU: `world` separately allocated blocks stand in for the peers' symmetric-memory blocks (on a
+    multi-GPU box the same addresses are NVLink mappings).  The fused exchange+merge must equal lmi_merge_ranks on
+    the gathered blocks -- ties by (probe rank, GPU rank), or by GPU rank without probe ranks -- and the gather
+    must reproduce every block byte for byte."""
+    from learnedmetricindex_b200 import _native
+
+    L = _native.lib()
+    rs = np.random.RandomState(9)
+    dev = torch.device("cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    for world, nq, k in [(2, 257, 10), (8, 1000, 10), (5, 33, 7), (32, 64, 10), (3, 1, 10)]:
+        d = rs.randint(0, 6, size=(world, nq, k)).astype(np.float64) / 4.0
+        p = rs.randint(0, 5, size=(world, nq, k)).astype(np.uint16)
+        ids = rs.randint(1, 1 << 30, size=(world, nq, k)).astype(np.uint32)
+        for w in range(world):
+            for q in range(nq):
+                o = np.lexsort((p[w, q], d[w, q]))
+                d[w, q], p[w, q], ids[w, q] = d[w, q][o], p[w, q][o], ids[w, q][o]
+        off_i, off_p = nq * k * 8, nq * k * 12
+        per_rank = -(-(off_p + nq * k * 2) // 16) * 16
+        blocks = []
+        for w in range(world):
+            raw = np.zeros(per_rank, dtype=np.uint8)
+            raw[:off_i] = d[w].reshape(-1).view(np.uint8)
+            raw[off_i:off_p] = ids[w].reshape(-1).view(np.uint8)
+            raw[off_p:off_p + nq * k * 2] = p[w].reshape(-1).view(np.uint8)
+            blocks.append(torch.from_numpy(raw).to(dev))
+        base = torch.tensor([b.data_ptr() for b in blocks], dtype=torch.int64, device=dev)
+
+        # gather: dst[w * bytes + i] = rank_base[w][i]
+        gathered = torch.full((world * per_rank,), 0xAB, dtype=torch.uint8, device=dev)
+        _native.check(L.lmi_gather_peer(base.data_ptr(), per_rank, world, gathered.data_ptr(), st), "lmi_gather_peer")
+        torch.cuda.synchronize()
+        assert torch.equal(gathered, torch.cat(blocks)), (world, nq, k)
+
+        td, ti, tp = (torch.from_numpy(a).to(dev) for a in (d, ids.view(np.int32), p.view(np.int16)))
+        for with_probe in (True, False):
+            exp_d = torch.empty((nq, k), dtype=torch.float64, device=dev)
+            exp_i = torch.empty((nq, k), dtype=torch.int32, device=dev)
+            _native.check(L.lmi_merge_ranks(td.data_ptr(), ti.data_ptr(), tp.data_ptr() if with_probe else None,
+                                            nq * k, nq * k, nq * k, world, nq, k, exp_d.data_ptr(), exp_i.data_ptr(),
+                                            st), "lmi_merge_ranks")
+            got_d = torch.full((nq, k), -1.0, dtype=torch.float64, device=dev)
+            got_i = torch.full((nq, k), -1, dtype=torch.int32, device=dev)
+            _native.check(L.lmi_merge_ranks_peer(base.data_ptr(), off_i, off_p if with_probe else -1, world, nq, k,
+                                                 got_d.data_ptr(), got_i.data_ptr(), st), "lmi_merge_ranks_peer")
+            torch.cuda.synchronize()
+            assert torch.equal(got_d, exp_d) and torch.equal(got_i, exp_i), (world, nq, k, with_probe)
+            # and against the definition, independent of either kernel
+            gd, gi = got_d.cpu().numpy(), got_i.cpu().numpy().view(np.uint32)
+            for q in range(0, nq, max(1, nq // 40)):
+                fd = d[:, q].reshape(-1)
+                fp = p[:, q].reshape(-1).astype(np.int64) if with_probe else np.zeros(world * k, dtype=np.int64)
+                o = np.lexsort((np.tile(np.arange(k), world), np.repeat(np.arange(world), k), fp, fd))[:k]
+                np.testing.assert_array_equal(gd[q], fd[o])
+                np.testing.assert_array_equal(gi[q], ids[:, q].reshape(-1)[o])

@@ -336,6 +336,55 @@ def test_shared_gate_changes_the_partial_lists_only(monkeypatch):
             assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1]), (impl, B, k)
 
 
+def test_gate_keeps_ties_at_zero_similarity(monkeypatch):
+    """All-zero queries (padding, empty embeddings) score exactly 0.0 against every row, so every list's bound is
+    0.0 and every candidate ties with it: the lower-row candidates of a range or column half that runs behind must
+    still get through the gate (a relative nudge of the bound vanishes at 0.0).  Expected: distance 1.0 and the
+    first ten rows of the first probed bucket, with the shared gate on and off, on every scan kernel."""
+    monkeypatch.setenv("LMI_RANGE_ROWS", "1024")
+    from learnedmetricindex_b200 import DeviceBucketLayout
+    from tests.golden_util import seeded_layers
+
+    rs = np.random.RandomState(3)
+    C, nq, d = 4, 300, 128
+    sizes = np.array([9000, 700, 12000, 3000])
+    X = rs.standard_normal((int(sizes.sum()), d)).astype(np.float32)
+    X = (X / np.linalg.norm(X, axis=1, keepdims=True)).astype(np.float16)
+    X[rs.rand(len(X)) < 0.01] = 0  # a few all-zero rows: they tie at 0.0 for ordinary queries as well
+    pred = rs.permutation(np.repeat(np.arange(C), sizes)).astype(np.int64)
+    Q = rs.standard_normal((nq, d)).astype(np.float32)
+    Q = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float16)
+    zero = np.arange(nq) % 3 == 0
+    Q[zero] = 0
+    layers = seeded_layers(7, "MLP", d, C, scale=2.0)
+    layout = DeviceBucketLayout.from_host(X, pred, C)
+    qd = torch.from_numpy(Q).cuda()
+    off = layout.bucket_off_host
+    ids = layout.ids.cpu().numpy()
+    for B, k in [(1, 10), (3, 10), (C, 10)]:
+        results = {}
+        for impl in (1, 0, 2, 3, 4):
+            for share in ("1", "0"):
+                monkeypatch.setenv("LMI_SCAN_SHARE_GATE", share)
+                li = _index(layers, C, scan_impl=impl)
+                li.attach_layout(layout)
+                for rep in range(3):
+                    dd, ii = li.search_device(qd, qd, [C], B, k)
+                    torch.cuda.synchronize()
+                    results[(impl, share, rep)] = (dd.cpu().numpy().copy(), ii.cpu().numpy().copy())
+        order = li.last_bucket_order.cpu().numpy()
+        ref_d, ref_i = results[(0, "0", 0)]
+        for key, (dd, ii) in results.items():
+            # the tensor-core kernels agree bit for bit on every query; the CUDA-core kernel sums in another
+            # order (last-ulp differences on ordinary queries), so it is held to the zero queries only
+            rows = zero if key[0] == 1 else slice(None)
+            assert np.array_equal(dd[rows], ref_d[rows]) and np.array_equal(ii[rows], ref_i[rows]), (B, k, key)
+        assert (ref_d[zero] == 1.0).all()
+        for q in np.nonzero(zero)[0][:50]:
+            b0 = int(order[q, 0])
+            assert np.array_equal(ref_i[q].view(np.uint32), ids[off[b0]: off[b0] + 10]), (B, q)
+
+
 def test_f32_queries_and_float_inputs():
     """f32 host inputs (the reference's documented dtype) take the cast path."""
     n, nq, C, B = 8000, 300, 8, 2
@@ -633,6 +682,44 @@ def test_graph_replay_equals_eager_launches():
     e3, j3, _ = li.search(None, Q[:1], X, Q[:1], pred, [C], n_buckets=1)
     np.testing.assert_array_equal(d3, e3)
     np.testing.assert_array_equal(i3, j3)
+
+
+def test_graph_cache_is_keyed_on_shapes_not_addresses():
+    """A caller that passes a NEW device tensor per call must keep replaying the one captured graph (the
+    inputs are copied into the entry's static buffers), and an entry that was evicted from the 8-entry
+    cache and comes back -- after more batch shapes than the workspace caches hold -- is re-captured on
+    live workspaces, never replayed on freed ones."""
+    from learnedmetricindex_b200.LearnedIndex import GRAPH_CACHE, WS_CACHE
+
+    n, nq, C, B = 20_000, 200, 9, 3
+    X, Q, layers, pred = _synthetic(n, 4 * nq, C, steps=40)
+    li = _index(layers, C)
+    li.prepare(X, pred, [C])
+    Qd = torch.from_numpy(np.ascontiguousarray(Q)).cuda()
+    keep = []  # hold the tensors so every call really sees a different address
+    for j in range(4):
+        q = Qd[j * nq:(j + 1) * nq].clone()
+        keep.append(q)
+        d, i, _ = li.search_graphed(q, q, [C], B, 10)
+        e, f = li.search_device(q, q, [C], B, 10)
+        torch.cuda.synchronize()
+        assert torch.equal(d, e) and torch.equal(i, f), j
+        assert len(li._graphs) == 1
+    assert len({t.data_ptr() for t in keep}) == 4
+    # more shapes than either cache holds, then the first shape again
+    first = Qd[:nq]
+    exp_d, exp_i = [t.clone() for t in li.search_device(first, first, [C], B, 10)]
+    for m in range(1, max(GRAPH_CACHE, WS_CACHE) + 3):
+        q = Qd[: nq + m]
+        d, i, _ = li.search_graphed(q, q, [C], B, 10)
+        e, f = li.search_device(q, q, [C], B, 10)
+        torch.cuda.synchronize()
+        assert torch.equal(d, e) and torch.equal(i, f), m
+    assert len(li._graphs) == GRAPH_CACHE
+    for rep in range(2):
+        d, i, _ = li.search_graphed(first, first, [C], B, 10)
+        torch.cuda.synchronize()
+        assert torch.equal(d, exp_d) and torch.equal(i, exp_i), rep
 
 
 def test_full_size_properties_10m():
