@@ -5,12 +5,20 @@ north_star asks for.  Buckets are independent units, so whole buckets are assign
 ranks; MLP weights and the query batch are replicated; every rank runs the single-GPU
 path (``LearnedIndex.search_device``) over the buckets it owns -- a probed bucket that
 lives elsewhere is an empty bucket locally and yields the reference's "no candidate"
-filler (id 0, +inf; LearnedIndex.py:340-341) -- and the only exchange step is ONE
-all-gather of the per-rank ``[nq, k]`` results (``nq*k*12`` bytes per rank; 1.2 MB at
-10k x 10) over NCCL/NVLink followed by ``lmi_merge_ranks`` on every rank.
+filler (id 0, +inf; LearnedIndex.py:340-341) -- and the only exchange step moves the per-rank
+``[nq, k]`` results (``nq*k*14`` bytes per rank with the probe ranks; 1.4 MB at 10k x 10).
 
-The all-gather buffer is packed ``[dists f64 | nns u32]`` per rank and the local merge
-kernel writes straight into this rank's send slot, so there is no staging copy.
+Two exchange paths, bit-identical results:
+  * ``exchange="peer"`` (the default where symmetric memory works): every rank writes its packed block
+    ``[dists f64 | nns u32 | probe u16]`` into symmetric memory, a device-side barrier orders the writes,
+    and ``lmi_merge_ranks_peer`` reads the peers' blocks over NVLink INSIDE the merge kernel -- no
+    collective-library call on the data path.  Navigation is query-sharded the same way (each rank infers
+    1/world of the batch, ``lmi_gather_peer`` collects the bucket order), and ``search_graphed`` replays
+    the whole sharded search as one CUDA graph.
+  * ``exchange="nccl"`` (fallback, agreed on by all ranks together): ONE all-gather of the packed blocks
+    followed by ``lmi_merge_ranks`` on every rank.
+
+The local merge kernel writes straight into this rank's send block, so there is no staging copy.
 
 Host-side logic (partitioning, buffer packing, gather, merge order) is backend-agnostic:
 ``tests/test_sharded_gloo.py`` runs it with world_size 2 over gloo on CPU, injecting a
@@ -18,11 +26,14 @@ numpy merge in place of the CUDA kernel.
 """
 from __future__ import annotations
 
+from collections import OrderedDict
 from typing import Callable, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
 import torch.distributed as dist
+
+SHARDED_GRAPH_CACHE = 8  # captured (shape, budget) entries kept per sharded index, least recently used goes first
 
 
 def partition_buckets(sizes: Sequence[int], world: int, weights: Optional[Sequence[float]] = None,
@@ -271,7 +282,7 @@ class ShardedLearnedIndex:
         # "nccl": all-gather + lmi_merge_ranks (GatherBuffers; also what the gloo tests run)
         self.exchange = exchange or os.environ.get("LMI_EXCHANGE", "peer")
         self._bufs = {}
-        self._graphs = {}
+        self._graphs = OrderedDict()
         if self.exchange == "peer" and self.world > 1 and torch.device(local.device).type == "cuda":
             self.exchange = "peer" if self._agree_on_peer_memory(local.device, group) else "nccl"
 
@@ -358,14 +369,28 @@ class ShardedLearnedIndex:
         host_in = not (isinstance(qn, torch.Tensor) and qn.is_cuda)
         dt = lambda x: (x.dtype if isinstance(x, torch.Tensor) else
                         (torch.float16 if np.asarray(x).dtype == np.float16 else torch.float32))
-        if not host_in:  # device matrices are read in place: the graph is keyed on their addresses
+        if not host_in:
             assert qn.is_contiguous() and qs.is_contiguous()
+        # The key must be the same on every rank: creating an instance is a collective (symmetric-memory
+        # rendezvous, an eager run with device barriers), so a rank that hit its cache while another missed
+        # would leave the job hanging.  It therefore holds shapes, dtypes and the budget only -- never a device
+        # address, which is per-rank allocator state; device inputs are copied into a static buffer instead.
         key = (nq, tuple(np.shape(qn)), dt(qn), tuple(np.shape(qs)), dt(qs), shared, host_in, tuple(n_categories),
-               int(n_buckets), int(k), 0 if host_in else qn.data_ptr(), 0 if host_in else qs.data_ptr())
+               int(n_buckets), int(k))
         entry = self._graphs.get(key)
         if entry is None:
+            while len(self._graphs) >= SHARDED_GRAPH_CACHE:
+                # least recently used first (every rank sees the same call sequence, so all evict the same
+                # entry); the graphs go before the workspaces and symmetric blocks they point into
+                _, old = self._graphs.popitem(last=False)
+                for old_inst in old["instances"]:
+                    if old_inst is not None:
+                        old_inst.pop("graph", None)
+                        old_inst.clear()
             entry = dict(instances=[None, None], turn=0)
             self._graphs[key] = entry
+        else:
+            self._graphs.move_to_end(key)
         t = entry["turn"]
         entry["turn"] ^= 1
         inst = entry["instances"][t]
@@ -381,7 +406,8 @@ class ShardedLearnedIndex:
                         part = torch.from_numpy(np.ascontiguousarray(part))
                     dst = inst["send_" + name]
                     dst[: part.shape[0]].copy_(part.to(dst.dtype), non_blocking=True)
-                # device inputs are read in place (see the key)
+                else:  # device inputs: one device-to-device copy into the instance's static buffer
+                    inst["full_" + name].copy_(src, non_blocking=True)
 
         if inst is None:
             inst = {}
@@ -394,7 +420,7 @@ class ShardedLearnedIndex:
                     inst["pg_" + name] = pg
                     inst["send_" + name] = pg.send_block()[: per * row_bytes].view(dtypes[name]).view(per, shapes[name][1])
                 else:
-                    inst["full_" + name] = qn if name == "n" else qs
+                    inst["full_" + name] = torch.empty(shapes[name], dtype=dtypes[name], device=dev)
             inst["pg_order"] = PeerGather(per * int(n_buckets) * 4, self.world, dev, self.group, n_blocks=1)
             inst["res"] = PeerBuffers(nq, k_out, self.world, self.rank, dev, self.group, n_blocks=1)
             inst["out"] = (torch.empty((nq, k_out), dtype=torch.float64, device=dev),
@@ -427,6 +453,9 @@ class ShardedLearnedIndex:
             upload(inst)
             body(None)  # eager run: every rank executes the same barriers, lazy caches fill outside the capture
             torch.cuda.current_stream().synchronize()
+            # the graph holds raw pointers into the local index's batch workspace and navigation workspace; both
+            # caches evict on their own schedule, so the instance keeps them alive for as long as its graph
+            inst["keep"] = (getattr(self.local, "_last_ws", None), dict(self.local.root_model._fused_ws))
             inst["events"] = [torch.cuda.Event(enable_timing=True, external=True) for _ in range(5)]
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):

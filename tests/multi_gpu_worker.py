@@ -47,6 +47,30 @@ def main():
             # host-facing API (queries uploaded 1/world per rank and all-gathered; graph replay on the peer path)
             dh, ih, _ = eng.search(None, Q.cpu().numpy(), None, Q.cpu().numpy(), None, [C], n_buckets=B, k=k)
             assert np.array_equal(dh, exp_d.cpu().numpy()) and np.array_equal(ih.view(np.int32), exp_i.cpu().numpy())
+    # graph cache of the sharded search: keyed on shapes only (a fresh device tensor per call replays the same
+    # graph on every rank), bounded, and an entry that was evicted and returns -- after more batch shapes than
+    # the local workspace caches hold -- is captured again on live workspaces
+    from learnedmetricindex_b200.sharded import SHARDED_GRAPH_CACHE
+
+    li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
+    li.attach_layout(full.restrict_to_buckets(parts[rank]))
+    eng = ShardedLearnedIndex(li, exchange="peer")
+    exp_d, exp_i = ref.search_device(Q, Q, [C], 3, 10)
+    for rep in range(4):
+        q = Q.clone() if (rep + rank) % 2 else Q  # ranks disagree on which calls see a new address
+        dg, ig, _ = eng.search_graphed(q, q, [C], 3, 10)
+        assert torch.equal(dg, exp_d) and torch.equal(ig, exp_i), ("graph key", rep, rank)
+        assert len(eng._graphs) == 1
+    for m in range(1, SHARDED_GRAPH_CACHE + 3):
+        q = Q[: nq - m].contiguous()
+        e_d, e_i = ref.search_device(q, q, [C], 3, 10)
+        dg, ig, _ = eng.search_graphed(q, q, [C], 3, 10)
+        assert torch.equal(dg, e_d) and torch.equal(ig, e_i), ("graph cycle", m, rank)
+    assert len(eng._graphs) == SHARDED_GRAPH_CACHE
+    for rep in range(3):
+        dg, ig, _ = eng.search_graphed(Q, Q, [C], 3, 10)
+        assert torch.equal(dg, exp_d) and torch.equal(ig, exp_i), ("graph replay after eviction", rep, rank)
+    del eng, li
     # a batch that does not divide by the number of ranks (padded navigation / upload slices)
     for exchange in ("peer", "nccl"):
         li = LearnedIndex(layers, {}, [(i,) for i in range(C)])
