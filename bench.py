@@ -499,6 +499,7 @@ class CpuBaseline:
         finite = np.isfinite(d_cpu) & (np.abs(d_cpu) < 1e38)
         dist_bad = int(((rel > 1e-3) & finite & ok[:, None] & ~mism).sum())
         unexplained = 0
+        max_gap = 0.0  # largest |exact f64 distance of the GPU's object - oracle's entry| among the explained ones
         qs, js = np.nonzero(mism)
         row_of_id = None
         if qs.size:
@@ -511,20 +512,34 @@ class CpuBaseline:
                     continue
                 x = self.layout.vectors[sorter[pos]].astype(np.float64)
                 true_d = 1.0 - float(np.dot(x, self.Q[q].astype(np.float64)))
-                if abs(true_d - float(d_cpu[q, j])) > tie_abs:
+                gap = abs(true_d - float(d_cpu[q, j]))
+                if gap > tie_abs:
                     unexplained += 1
+                else:
+                    max_gap = max(max_gap, gap)
         n_ok = int(ok.sum())
         return {"bucket_order_rows_equal": float(rows_equal.mean()),
                 "bucket_order_rows_unexplained": int(unexplained_order),
                 "id_agreement": float((i_gpu[ok] == i_cpu[ok]).mean()) if n_ok else None,
                 "id_mismatches": int(mism.sum()), "unexplained": int(unexplained + unexplained_order + dist_bad),
                 "dists_beyond_rel_1e-3": dist_bad, "queries": int(nq),
+                "max_abs_dist_gap_of_explained_id_mismatches": max_gap, "tie_abs": tie_abs,
+                "max_rel_dist_error": float(rel[finite & ok[:, None] & ~mism].max()) if (finite & ok[:, None] & ~mism).any() else None,
                 "rule": f"ids equal except where the exact f64 distance of the returned object is within {tie_abs:g} "
                         f"of the oracle's entry (f32 rounding tie); bucket rows equal except probability ties <= {prob_tie:g}"}
 
 
 # --------------------------------------------------------------------------------------
 _REAL_STDOUT = None
+
+
+def bench_config(wl_name, n, nq, C, B, world):
+    """The `config` object of the JSON line -- built by this one function for BOTH arms (ours and
+    `--impl reference`), so the two lines describe the workload with identical keys and values; what only one
+    arm knows (recall, sharding, generator parameters) goes into the sibling key `config_detail`."""
+    return {"workload": wl_name, "n": n, "nq": nq, "d": D, "n_buckets_in_index": C, "probed_buckets": B, "k": K_NN,
+            "l2_policy": "inputs larger than L2 (bucket vectors %.1f GB over %d GPU(s), every probed bucket read "
+                         "once per step)" % (n * D * 2 / 1e9, world)}
 
 
 def emit_json(obj):
@@ -541,7 +556,7 @@ def emit_json(obj):
 # --------------------------------------------------------------------------------------
 # multi-level workload: `--workload ml`, single GPU
 # --------------------------------------------------------------------------------------
-def run_multilevel(args):
+def run_multilevel(args, emit=True):
     """The reference CLI's default tree shape (`--n-categories 10 10`, search/search.py:314) in the
     notebook's arrangement: a low-dimensional navigation representation (PCA of the 768-d vectors,
     search/search.py:192-216) routes through a 2-level tree of `MLP` models, the scan runs on the
@@ -641,7 +656,7 @@ def run_multilevel(args):
         parity = {"visit_order_rows_equal": float(same.mean()),
                   "id_agreement_on_equal_rows": float((i_h[:nc][same] == exp_i[same]).mean())}
 
-    emit_json({
+    out_ml = {
         "metric": "QPS, 2-level LMI", "value": args.nq / ms * 1e3, "unit": "QPS", "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "data": "synthetic",
         "dtype": "f16 in / f32 accumulate (scan), tf32 x3 split / f32 accumulate (MLPs)",
@@ -651,7 +666,10 @@ def run_multilevel(args):
         "kernel_ms": {"navigation": stage[0], "invert": stage[1], "scan": stage[2], "merge": stage[3]},
         "e2e": {"value": args.nq / e2e_ms * 1e3, "unit": "QPS", "ms_per_step": e2e_ms},
         "cpu_baseline": cpu, "parity_vs_oracle": parity,
-    })
+    }
+    if emit:
+        emit_json(out_ml)
+    return out_ml
 
 
 def main():
@@ -682,6 +700,17 @@ def main():
                     help="time limit (s) of the ONE unmodified li.LearnedIndex.search call")
     ap.add_argument("--no-workload-c", action="store_true",
                     help="skip the appended 100M x 768 measurement (BASELINE.json configs[2])")
+    ap.add_argument("--only-headline", action="store_true",
+                    help="the headline measurement alone: no CPU leg, no appended workloads, sweeps or cold call "
+                         "(what the ncu passes run)")
+    ap.add_argument("--no-workload-ml", action="store_true",
+                    help="skip the appended 2-level (n_categories 10 10) measurement, the reference CLI's default tree")
+    ap.add_argument("--no-config-a", action="store_true",
+                    help="skip the appended 100k x 768 measurement (BASELINE.json configs[0])")
+    ap.add_argument("--no-sweeps", action="store_true",
+                    help="skip the appended budget sweep (configs[3]) and batch sweep (configs[4])")
+    ap.add_argument("--no-cold-call", action="store_true",
+                    help="skip the cold-call measurement (first search() of a fresh index from host data)")
     ap.add_argument("--sweep", default="", help="comma list of B values: print recall/QPS per B to stderr")
     ap.add_argument("--balance", default="size2", choices=["calibrated", "size2"],
                     help="--shard buckets: LPT cost = rows^2 (queries follow the data; measured the more robust of the "
@@ -694,6 +723,9 @@ def main():
     ap.add_argument("--ml-model-type", default="MLP", help="--workload ml: model type of every tree node")
     ap.add_argument("--ml-cpu-queries", type=int, default=2000, help="--workload ml: queries of the cpu_baseline leg")
     args = ap.parse_args()
+    if args.only_headline:
+        args.no_cpu_baseline = args.no_workload_c = args.no_workload_ml = args.no_config_a = True
+        args.no_sweeps = args.no_cold_call = True
     args.default_sizes = not (args.n or args.nq or args.buckets)  # before the workload defaults are filled in
     if args.probe is None:
         args.probe = 10 if args.workload == "ml" else 4
@@ -738,12 +770,51 @@ def main():
         ac.steps, ac.warmup = min(args.steps, 10), 3
         try:
             oc = measure(ac, WORKLOADS["c"]["name"], device, rank, world, local_rank, headline=False)
-            keep = ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "e2e",
+            keep = ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "config_detail", "e2e",
                     "kernel_ms", "roofline", "clocks", "gpu_launches", "host_enqueue_ms_per_step", "multi_gpu_parity")
             out["workload_c"] = {k_: oc[k_] for k_ in keep if k_ in oc}
         except Exception as e:  # noqa: BLE001 -- the headline stands; say why the 100M point is absent
             log(f"workload c failed: {e!r}")
             out["workload_c"] = {"error": repr(e)}
+    # BASELINE.json configs[0] (the reference's own CPU-runnable size, 100k x 768) on the same line at N = 1, with
+    # the unmodified reference as the checker of the timed result
+    if args.workload == "b" and args.default_sizes and world == 1 and not args.no_config_a:
+        import copy
+        import gc
+
+        gc.collect()
+        torch.cuda.empty_cache()
+        aa = copy.copy(args)
+        aa.workload, aa.n, aa.shard = "a", WORKLOADS["a"]["n"], "auto"
+        try:
+            oa = measure(aa, WORKLOADS["a"]["name"], device, rank, world, local_rank, headline=False,
+                         check_unmodified=True)
+            keep = ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "config", "config_detail", "e2e",
+                    "kernel_ms", "roofline", "gpu_launches", "host_enqueue_ms_per_step", "parity_vs_reference")
+            out["config_a"] = {k_: oa[k_] for k_ in keep if k_ in oa}
+        except SystemExit:
+            raise
+        except Exception as e:  # noqa: BLE001
+            log(f"config a failed: {e!r}")
+            out["config_a"] = {"error": repr(e)}
+        gc.collect()
+        torch.cuda.empty_cache()
+    # the reference CLI's default tree shape (--n-categories 10 10, search/search.py:314) on the same line at N = 1
+    if args.workload == "b" and args.default_sizes and world == 1 and not args.no_workload_ml:
+        import copy
+        import gc
+
+        am = copy.copy(args)
+        am.workload, am.n, am.nq, am.buckets, am.probe = "ml", WORKLOADS["ml"]["n"], WORKLOADS["ml"]["nq"], \
+            WORKLOADS["ml"]["buckets"], 10
+        am.steps = min(args.steps, 20)
+        try:
+            out["workload_ml"] = run_multilevel(am, emit=False)
+        except Exception as e:  # noqa: BLE001
+            log(f"workload ml failed: {e!r}")
+            out["workload_ml"] = {"error": repr(e)}
+        gc.collect()
+        torch.cuda.empty_cache()
     if rank == 0:
         emit_json(out)
     if world > 1:
@@ -768,7 +839,7 @@ def result_checksum(d, i):
     return int((a ^ (b << 1)).item())
 
 
-def measure(args, wl_name, device, rank, world, local_rank, headline):
+def measure(args, wl_name, device, rank, world, local_rank, headline, check_unmodified=False):
     """Build the workload ``args`` describes over the ``world`` ranks, check it, time it; returns the JSON object.
     ``headline=False`` (the appended 100M point) skips the CPU leg, the budget search and the sweeps."""
     if args.shard == "auto":
@@ -1008,6 +1079,114 @@ def measure(args, wl_name, device, rank, world, local_rank, headline):
                    "with the burst cuBLAS peak (best of 10, timed alone); `frac` above is the mean over the timed "
                    "region, where the board sits at its power cap"}
 
+    # ---- BASELINE.json configs[3] and configs[4] on the same line (single GPU, same index): the candidate-budget
+    # sweep (probed buckets -> recall@10, QPS, the scan's roofline) and the query-batch sweep (1 ... 100k queries:
+    # device time of one graph replay, host-to-host latency of `search` with pinned host queries) ----
+    sweep_d = sweep_e = None
+    if headline and world == 1 and not args.no_sweeps:
+        from learnedmetricindex_b200 import synthetic as syn
+
+        def quick(Qx, Bx, steps=5):
+            """(graph ms/step, mean scan launch ms, scan roofline dict) of searches of Qx with budget Bx."""
+            nqx = Qx.shape[0]
+            for _ in range(3):
+                li.search_graphed(Qx, Qx, [C], Bx, K_NN)
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            a0.record()
+            for _ in range(steps):
+                li.search_graphed(Qx, Qx, [C], Bx, K_NN)
+            a1.record()
+            torch.cuda.synchronize()
+            g_ms = a0.elapsed_time(a1) / steps
+            evx = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(steps)]
+            li.search_device(Qx, Qx, [C], Bx, K_NN)
+            for e in evx:
+                li.search_device(Qx, Qx, [C], Bx, K_NN, events=e)
+            torch.cuda.synchronize()
+            sc_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evx]))
+            cnt = li.last_plan["counts"].cpu().numpy().astype(np.int64)
+            fl = 2.0 * D * float((cnt * sizes_local).sum())
+            by = 2.0 * D * float(sizes_local[cnt > 0].sum()) + 2.0 * D * nqx * Bx + 8.0 * nqx * K_NN
+            tt, th = fl / (tf_burst * 1e12), by / (hbm_peak * 1e9)
+            rf = {"bound": "tensor" if tt >= th else "hbm", "roofline_ms": max(tt, th) * 1e3, "scan_ms": sc_ms,
+                  "frac": max(tt, th) * 1e3 / sc_ms}
+            return g_ms, sc_ms, rf
+
+        try:
+            sweep_d = []
+            for Bs in (1, 2, 3, 4, 6, 8, 16, 48, 120):
+                if Bs > C:
+                    continue
+                rs_ = recall_at_10(run_once(Bs)[1], gt)
+                g_ms, sc_ms, rf = quick(Q, Bs)
+                sweep_d.append({"probed_buckets": Bs, "recall_at_10": rs_, "qps": nq / (g_ms / 1e3), "ms_per_step": g_ms,
+                                "scan": rf})
+                log(f"sweep_d B={Bs}: recall {rs_:.4f} QPS {nq / (g_ms / 1e3):.0f} scan {sc_ms:.3f} ms "
+                    f"({rf['bound']}, frac {rf['frac']:.3f})")
+        except Exception as e:  # noqa: BLE001
+            sweep_d = {"error": repr(e)}
+        try:
+            sweep_e = []
+            Qbig = syn.make_vectors(100_000, w["spec"], device=device, stream=2)
+            for nqx in (1, 10, 100, 1000, 10_000, 100_000):
+                Qx = Qbig[:nqx].contiguous()
+                g_ms, sc_ms, rf = quick(Qx, B)
+                Qxh = torch.empty(Qx.shape, dtype=Qx.dtype).pin_memory()
+                Qxh.copy_(Qx.cpu())
+                lat = []
+                for r_ in range(3 + 10):
+                    t0 = time.perf_counter()
+                    li.search(None, Qxh, None, Qxh, None, [C], n_buckets=B, k=K_NN)
+                    lat.append(time.perf_counter() - t0)
+                sweep_e.append({"nq": nqx, "probed_buckets": B, "device_ms_per_batch": g_ms, "qps_device": nqx / (g_ms / 1e3),
+                                "host_to_host_ms_median": float(np.median(lat[3:]) * 1e3),
+                                "qps_host_to_host": nqx / float(np.median(lat[3:])), "scan": rf})
+                log(f"sweep_e nq={nqx}: device {g_ms:.3f} ms, host-to-host {np.median(lat[3:]) * 1e3:.3f} ms "
+                    f"scan {sc_ms:.3f} ms ({rf['bound']}, frac {rf['frac']:.3f})")
+            del Qbig
+        except Exception as e:  # noqa: BLE001
+            sweep_e = {"error": repr(e)}
+        li.search_device(Q, Q, [C], B, K_NN)  # last_plan / last_bucket_order back on the headline batch
+        torch.cuda.synchronize()
+
+    # ---- cold call (SURVEY.md section 8d): the FIRST search() of a fresh index object through the reference-facing
+    # signature with HOST data -- bucket layout build (the regrouping the reference pays on every call,
+    # LearnedIndex.py:350,357), its H2D, weight splits, workspace allocation, graph capture and the search itself
+    cold = None
+    if headline and world == 1 and not args.no_cold_call:
+        try:
+            import psutil
+
+            need = w["vectors"].numel() * 2
+            if psutil.virtual_memory().available < 2.5 * need or torch.cuda.mem_get_info()[0] < 1.3 * need:
+                cold = {"skipped": "not enough free host RAM / HBM for a second copy of the index"}
+            else:
+                Xh = w["vectors"].cpu().numpy()  # host matrix (bucket-major order here; any order works)
+                pred_h = np.repeat(np.arange(C, dtype=np.int64), np.diff(w["bucket_off"]))[:, None]
+                Qn = Qh.numpy()
+                li_cold = LearnedIndex(w["layers"], {}, [(i,) for i in range(C)])
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                d_c, i_c, tm_c = li_cold.search(None, Qn, Xh, Qn, pred_h, [C], n_buckets=B, k=K_NN)
+                cold_s = time.perf_counter() - t0
+                t0 = time.perf_counter()
+                d_w, _, _ = li_cold.search(None, Qn, Xh, Qn, pred_h, [C], n_buckets=B, k=K_NN)
+                warm_s = time.perf_counter() - t0
+                assert np.array_equal(d_c, d_e2e) and np.array_equal(d_w, d_e2e), "cold-call distances differ"
+                cold = {"cold_call_s": cold_s, "second_call_s": warm_s, "host_bytes_uploaded": int(need),
+                        "what": "first LearnedIndex.search(host data_search, data_prediction, host queries) of a new "
+                                "index object: layout build + H2D + weight split + workspace + graph capture + search; "
+                                "distances equal the timed steps'"}
+                log(f"cold call {cold_s:.2f}s, second call {warm_s * 1e3:.2f} ms")
+                del li_cold, Xh, pred_h
+                import gc
+
+                gc.collect()
+                torch.cuda.empty_cache()
+        except Exception as e:  # noqa: BLE001 -- the steady-state numbers stand
+            cold = {"error": repr(e)}
+
     # ---- CPU baseline (rank 0, N == 1 only): the oracle port on the WHOLE batch, which doubles as the
     # asserted parity check of the timed GPU result at the headline size ----
     cpu = parity = None
@@ -1025,6 +1204,33 @@ def measure(args, wl_name, device, rank, world, local_rank, headline):
             del cb
         except Exception as e:  # the GPU numbers stand; say why the CPU leg is absent
             cpu = {"value": None, "unit": "QPS", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
+
+    # ---- config A only: the timed GPU result checked against ONE call of the UNMODIFIED reference
+    # (li.LearnedIndex.search out of oracle/_ref, with oracle/faiss_shim for the absent faiss) on all queries --
+    # the size at which the reference itself finishes in about a second -- and against the oracle port ----
+    unmodified = None
+    if check_unmodified and rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            cb = CpuBaseline(w, C)
+            t_port, d_p, i_p, order_p = cb.run(B)
+            par_port = cb.explain(d_p, i_p, order_p, d_e2e, i_e2e, order_gpu)
+            unmodified = {"oracle_port": {"seconds": t_port, "qps": nq / t_port, "cores": cb.threads,
+                                          "parity": par_port}}
+            if cb.unmodified_available():
+                t_u, d_u, i_u, _ = cb.run_unmodified(B, limit_s=args.reference_limit)
+                par_u = cb.explain(d_u, i_u.astype(np.uint32), order_p, d_e2e, i_e2e, order_gpu)
+                unmodified["unmodified_reference"] = {
+                    "seconds": t_u, "qps": nq / t_u, "kind": "reference", "parity": par_u,
+                    "ids_equal_to_port": float((i_u.astype(np.uint32) == i_p).mean()),
+                    "what": "one call of li.LearnedIndex.search (oracle/_ref, unmodified) on all queries"}
+                parity = par_u if parity is None else parity
+            else:
+                unmodified["unmodified_reference"] = {"note": "oracle/_ref not staged (python -m oracle.build_ref)"}
+                parity = par_port if parity is None else parity
+            log(f"config A parity: {unmodified}")
+            del cb
+        except Exception as e:  # noqa: BLE001
+            unmodified = {"error": repr(e)}
 
     # ---- the metric's other reading: the SMALLEST budget whose recall@10 is still >= 0.90;
     # the headline `value` stays on the README's budget (`--probe`, 4 of 120 buckets) ----
@@ -1046,12 +1252,13 @@ def measure(args, wl_name, device, rank, world, local_rank, headline):
         "metric": "QPS at recall@10>=0.90", "value": value, "unit": "QPS", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f16 in / f32 accumulate (scan), tf32 x3 split / f32 accumulate (MLP)", "data": "synthetic",
-        "config": {"workload": wl_name, "n": args.n, "nq": nq, "d": D, "n_buckets_in_index": C, "probed_buckets": B,
-                   "k": K_NN, "recall_at_10": recall, "sharding": (f"equal row slices of every bucket over {world} GPU(s)" if args.shard == "rows" and world > 1
-                                else f"buckets over {world} GPU(s)"),
-                   "l2_policy": "inputs larger than L2 (bucket vectors %.1f GB per GPU, read once per step)"
-                                % (w["vectors"].numel() * 2 / 1e9),
-                   "synthetic": {"centres": args.centres, "latent_dim": args.latent, "noise": args.noise}},
+        "config": bench_config(wl_name, args.n, nq, C, B, world),
+        "config_detail": {
+            "recall_at_10": recall,
+            "sharding": (f"equal row slices of every bucket over {world} GPU(s)" if args.shard == "rows" and world > 1
+                         else f"buckets over {world} GPU(s)"),
+            "bucket_vectors_gb_this_gpu": w["vectors"].numel() * 2 / 1e9,
+            "synthetic": {"centres": args.centres, "latent_dim": args.latent, "noise": args.noise}},
         "e2e": {"value": e2e_qps, "unit": "QPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_s / K * 1e3},
         "gpu_launches": launches_per_step * K,
@@ -1066,6 +1273,10 @@ def measure(args, wl_name, device, rank, world, local_rank, headline):
         "multi_gpu_parity": multi,
         "clocks": clocks,
         "smallest_budget_with_recall_0.90": min_point,
+        "cold_call": cold,
+        "parity_vs_reference": unmodified,
+        "sweep_d": sweep_d,
+        "sweep_e": sweep_e,
     }
     if parity is not None and parity["unexplained"] > 0:
         # a fast kernel whose results differ from the reference's is not done: print the line, then fail
@@ -1140,8 +1351,7 @@ def run_reference(args, wl_name, rank, world, local_rank):
         "impl": "reference", "metric": "QPS at recall@10>=0.90", "value": qps, "unit": "QPS", "n_gpus": args.gpus,
         "steps": K, "warmup": W, "ms_per_step": total / K * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl_name, "n": args.n, "nq": nq, "d": D, "n_buckets_in_index": C, "probed_buckets": B,
-                   "k": K_NN},
+        "config": bench_config(wl_name, args.n, nq, C, B, args.gpus),
         "cpu_baseline": {"value": qps, "unit": "QPS", "cores": cb.threads, "kind": "port", "sample": sample,
                          "host_cpus": host_threads(), "host_ram_gib": round(cb.ram_gb, 1), **extra},
         "e2e": {"value": qps, "unit": "QPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
