@@ -39,6 +39,7 @@ LISTS_PER_ITEM = 2  # LMI_LISTS_PER_ITEM: partial top-10 lists a scan work item 
 SCAN_ROWS_PER_TILE = 64
 SCAN_MAX_D = 768  # widest search representation the tcgen05 scan kernels take (lmi_scan.cu: SCAN_MAX_D)
 DEFAULT_RANGE_ROWS = 24576  # upper bound on the rows of a scan work item (see plan_scan; sustained 10M sweep: 8192 +5 %, 16384 0, 24576 -1.9 %, 32768 -1.0 %)
+RANGE_DIV_FULL_TILES, RANGE_DIV_SPARSE_TILES, RANGE_DIV_FEW_QUERIES = 1.5, 3.0, 6.0  # plan_scan: long items per SM
 DEFAULT_SCAN_IMPL = 0
 GRAPH_CACHE = 8  # captured (shape, budget) combinations kept per index (least recently used goes first)
 WS_CACHE = 8  # batch shapes whose workspace is kept
@@ -74,7 +75,17 @@ def plan_scan(nq: int, n_probe: int, n_buckets_in_index: int, n_rows: int, max_b
     rows_per_sm = tiles * mean_bucket / max(1, n_sms)  # rows (x 128 queries) one CTA scans in the launch
     floor_rows = max(1024, -(-max_bucket // MAX_RANGES))
     env = os.environ.get
-    main = int(env("LMI_RANGE_ROWS", 0)) or int(min(DEFAULT_RANGE_ROWS, max(rows_per_sm / 6.0, 2048.0)))
+    # long items per SM the main cut aims for.  Measured on a B200 (tools/shard_plan_lab.py,
+    # profiles/r03_shard_plan_lab_*.jsonl): where the query tiles are full (>= 128 probing queries per bucket:
+    # the tensor-bound regime) few, long items win -- a 1/8 bucket shard of the 10M index scans in 0.70 ms with
+    # 1.5 items per SM against 0.87-1.06 ms with 6 (every item re-gathers its 128 queries into tensor memory and
+    # re-warms its top-10, and the two-level cut below evens out the end of the launch anyway); batches that
+    # leave the tiles mostly empty are HBM bound and want more items in flight (3: -3 % at 100-1000 queries);
+    # a handful of queries keeps the finest cut so that every SM streams.
+    per_bucket = pairs / local
+    div = float(env("LMI_RANGE_DIV", 0)) or (RANGE_DIV_FULL_TILES if per_bucket >= 128 else
+                                             RANGE_DIV_SPARSE_TILES if per_bucket >= 2 else RANGE_DIV_FEW_QUERIES)
+    main = int(env("LMI_RANGE_ROWS", 0)) or int(min(DEFAULT_RANGE_ROWS, max(rows_per_sm / div, 2048.0)))
     main = max(main, floor_rows)
     main = _round_up(min(main, max(max_bucket, rows_per_tile)), rows_per_tile)
     tail = int(env("LMI_TAIL_ROWS", 0)) or main // 3

@@ -111,6 +111,25 @@ def test_plan_scan(nq, B, C, n, maxb):
             assert -(-maxb // tail) <= 16  # <= 32 partial lists per probe: the merge's one-list-per-lane path
 
 
+def test_plan_scan_sharded_shapes_get_long_items_and_a_tail():
+    """A rank of a bucket-sharded index sees all queries but 1/world of the buckets: the cut must not fall back to
+    thousands of short items (measured on a B200, profiles/r03_shard_plan_lab_*.jsonl: 1/8 of the 10M index scans
+    in 0.70 ms with ~15k-row items and a short tail level, 0.87-1.06 ms with 3.7k-row items).  Few queries keep the
+    fine cut (HBM bound: every SM has to stream)."""
+    from learnedmetricindex_b200 import plan_scan
+
+    full = plan_scan(10000, 4, 120, 10_000_000, 113_656)
+    assert full["range_len"] == 24576 and full["tail_range_len"] == 8192  # the single-GPU headline cut is unchanged
+    for world in (2, 4, 8):
+        p = plan_scan(10000, 4, 120, 10_000_000 // world, 113_656, n_nonempty=120 // world)
+        assert p["range_len"] >= 12288 and 0 < p["tail_range_len"] < p["range_len"] and p["tail_permille"] > 0, (world, p)
+        assert p["rmax"] <= 16  # <= 32 partial lists per probe: the merge's one-list-per-lane path
+    few = plan_scan(10, 4, 120, 10_000_000, 113_656)
+    assert few["range_len"] <= 4096
+    mid = plan_scan(1000, 4, 120, 10_000_000, 113_656)
+    assert few["range_len"] < mid["range_len"] <= 24576
+
+
 def test_flat_bucket_ids_follow_groupby_key_order():
     """Multi-level layout: flat id == rank of the path in groupby(category_L1..L) key order
     (LearnedIndex.py:343-350); incomplete paths go to one trailing, unprobeable bucket."""
