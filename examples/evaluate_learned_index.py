@@ -62,13 +62,13 @@ def main():
     config = BuildConfiguration([algorithms["faiss_kmeans"]], args.epochs, args.model_type, args.lr, args.n_categories)
     builder = LearnedIndexBuilder(data_pd, config)
     li, data_prediction, n_buckets_in_index, build_t, cluster_t = builder.build()
-    LOG.info(f"Total number of buckets in the index: {n_buckets_in_index}")
-    LOG.info(f"Cluster time: {cluster_t}")
-    LOG.info(f"Pure build time: {build_t}")
-    LOG.info(f"Overall build time: {time.time() - s}")
+    LOG.info("index built: %d buckets", n_buckets_in_index)
+    LOG.info("  k-means assignment  %.2f s", cluster_t)
+    LOG.info("  training + routing  %.2f s", build_t)
+    LOG.info("  build, wall clock   %.2f s", time.time() - s)
 
     n_buckets = sorted({b for b in (int((p / 100) * n_buckets_in_index) for p in args.buckets_perc) if b > 0})
-    LOG.info(f"Number of buckets to search in: {n_buckets}")
+    LOG.info("probe budgets to evaluate: %s", n_buckets)
 
     # exact ground truth (Baseline.search semantics, search/li/Baseline.py:11-16: ids + 1)
     dev = li.device
@@ -77,7 +77,7 @@ def main():
 
     files = []
     for bucket in n_buckets:
-        LOG.info(f"Searching with {bucket} buckets")
+        LOG.info("--- budget: %s of %d buckets per query", bucket, n_buckets_in_index)
         dists, nns, measured_time = li.search(
             data_navigation=data_pd,
             queries_navigation=queries,
@@ -88,11 +88,11 @@ def main():
             n_buckets=bucket,
             k=args.k,
         )
-        LOG.info(f"Inference time: {measured_time['inference']}")
-        LOG.info(f"Search time: {measured_time['search']}")
-        LOG.info(f"Search within buckets time: {measured_time['search_within_buckets']}")
-        LOG.info(f"Sequential search time: {measured_time['seq_search']}")
-        LOG.info(f"Sort time: {measured_time['sort']}")
+        LOG.info("  navigation (MLP + top-B)   %.6f s", measured_time["inference"])
+        LOG.info("  whole call, host to host   %.6f s", measured_time["search"])
+        LOG.info("  inversion + scan + merge   %.6f s", measured_time["search_within_buckets"])
+        LOG.info("    of which the bucket scan %.6f s", measured_time["seq_search"])
+        LOG.info("    of which the merge       %.6f s", measured_time["sort"])
         LOG.info(f"Recall@{args.k}: {get_recall(nns.astype(np.int64), gt, args.k):.4f}")
         identifier = f"{kind}-learned-index-{'_'.join(map(str, args.n_categories))}-buckets={bucket}"
         files.append(store_results(os.path.join(args.out, kind, size, f"{identifier}.h5"), "Learned-index", kind,
